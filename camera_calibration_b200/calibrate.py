@@ -1,0 +1,358 @@
+"""Host-side mirror of the reference's interface for the LM refinement path.
+
+  Calibrator.refineCalibrationParameters   src/calibrate.py:117-171   (same signature / returns)
+  Calibrator.projectAllPoints              src/calibrate.py:190-197
+  Calibrator._compose/_decomposeParameterVector   src/calibrate.py:199-267
+  ProjectionJacobian.compute               src/jacobian.py:48-85      (parity only: dense J)
+  getSensorPoints                          src/calibrate.py:277-282
+
+Everything numeric runs in libcalib_b200.so on the GPU; there is no CPU fallback here.
+`Problem` is the thin object-oriented face of one C-ABI handle."""
+import ctypes
+import time
+
+import numpy as np
+
+from . import _lib
+from . import distortion
+from . import mathutils as mu
+from ._lib import CalibError, as_f64, dptr
+
+
+def flatten_detections(allDetections):
+    """list of (sensorPoints (Ni,2), modelPoints (Ni,3)) -> CSR (view_offsets, model, sensor)."""
+    counts = [len(m) for s, m in allDetections]
+    offs = np.zeros(len(counts) + 1, dtype=np.int64)
+    np.cumsum(counts, out=offs[1:])
+    N = int(offs[-1])
+    model = np.empty((N, 3), dtype=np.float64)
+    sensor = np.empty((N, 2), dtype=np.float64)
+    for i, (s, m) in enumerate(allDetections):
+        model[offs[i]:offs[i + 1]] = np.asarray(m, dtype=np.float64).reshape(-1, 3)
+        sensor[offs[i]:offs[i + 1]] = np.asarray(s, dtype=np.float64).reshape(-1, 2)
+    return offs, model, sensor
+
+
+def getSensorPoints(allDetections):
+    """src/calibrate.py:277-282"""
+    return flatten_detections(allDetections)[2]
+
+
+class Problem:
+    """One calibration problem resident on one GPU (a calib_t handle)."""
+
+    def __init__(self, model, view_offsets, model_pts, sensor_pts, device=0):
+        self.model = distortion.model_id_of(model)
+        self.L = 10 if self.model == distortion.RADTAN else 9
+        self.view_offsets = np.ascontiguousarray(view_offsets, dtype=np.int64)
+        self.M = len(self.view_offsets) - 1
+        self.N = int(self.view_offsets[-1]) if self.M >= 0 else 0
+        self.K = self.L + 6 * self.M
+        mp = as_f64(model_pts).reshape(-1, 3)
+        sp = as_f64(sensor_pts).reshape(-1, 2)
+        if len(mp) != self.N or len(sp) != self.N:
+            raise ValueError("view_offsets[-1] must equal the number of points")
+        self._L = _lib.lib()
+        self._h = ctypes.c_void_p()
+        rc = self._L.calib_create(ctypes.byref(self._h), self.model, self.M,
+                                  self.view_offsets.ctypes.data_as(ctypes.POINTER(ctypes.c_int64)),
+                                  dptr(mp), dptr(sp), int(device))
+        if rc != 0:
+            msg = self._L.calib_last_error(None)
+            self._h = None
+            raise CalibError(rc, msg.decode() if msg else "calib_create failed")
+
+    @classmethod
+    def from_detections(cls, model, allDetections, device=0):
+        offs, mp, sp = flatten_detections(allDetections)
+        return cls(model, offs, mp, sp, device)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.calib_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            msg = self._L.calib_last_error(self._h)
+            raise CalibError(rc, msg.decode() if msg else "")
+
+    def _P(self, P):
+        P = as_f64(P).ravel()
+        if P.size != self.K:
+            raise ValueError(f"Expected a parameter vector of {self.K} values, got {P.size}")
+        return P
+
+    def set_segment(self, n):
+        self._check(self._L.calib_set_segment(self._h, int(n)))
+
+    def project(self, P):
+        P = self._P(P)
+        y = np.empty((self.N, 2))
+        self._check(self._L.calib_project(self._h, dptr(P), dptr(y)))
+        return y
+
+    def cost(self, P):
+        P = self._P(P)
+        E = ctypes.c_double()
+        self._check(self._L.calib_cost(self._h, dptr(P), ctypes.cast(ctypes.byref(E), _lib._d)))
+        return E.value
+
+    def residual_jacobian(self, P):
+        P = self._P(P)
+        r = np.empty(2 * self.N)
+        Jc = np.empty((2 * self.N, self.L))
+        Jv = np.empty((2 * self.N, 6))
+        self._check(self._L.calib_eval_residual_jacobian(self._h, dptr(P), dptr(r), dptr(Jc), dptr(Jv)))
+        return r, Jc, Jv
+
+    def normal_equations(self, P):
+        P = self._P(P)
+        A = np.empty((self.L, self.L))
+        B = np.empty((self.M, self.L, 6))
+        D = np.empty((self.M, 6, 6))
+        g = np.empty(self.K)
+        E = ctypes.c_double()
+        self._check(self._L.calib_eval_normal_equations(
+            self._h, dptr(P), dptr(A), dptr(B), dptr(D), dptr(g), ctypes.cast(ctypes.byref(E), _lib._d)))
+        return A, B, D, g, E.value
+
+    def lm_step(self, P, lam):
+        P = self._P(P)
+        delta = np.empty(self.K)
+        self._check(self._L.calib_lm_step(self._h, dptr(P), float(lam), dptr(delta)))
+        return delta
+
+    def lm_run(self, P0, maxIters, lam0=1e-3, lam_min=1e-10, lam_max=1e10, err_min=1e-12,
+               want_trace=True):
+        """Returns (sse, P, iters, trace[iters,4])."""
+        P = self._P(P0).copy()
+        sse = ctypes.c_double()
+        iters = ctypes.c_int()
+        trace = np.zeros((max(int(maxIters), 1), 4)) if want_trace else None
+        self._check(self._L.calib_lm_run(
+            self._h, dptr(P), int(maxIters), lam0, lam_min, lam_max, err_min,
+            ctypes.cast(ctypes.byref(sse), _lib._d), ctypes.byref(iters),
+            dptr(trace) if want_trace else None))
+        return sse.value, P, iters.value, (trace[:iters.value].copy() if want_trace else None)
+
+    # resident variants (bench: device part alone)
+    def upload(self, P):
+        self._check(self._L.calib_upload_params(self._h, dptr(self._P(P))))
+
+    def lm_run_resident(self, maxIters, lam0=1e-3, lam_min=1e-10, lam_max=1e10, err_min=1e-12):
+        sse = ctypes.c_double()
+        iters = ctypes.c_int()
+        self._check(self._L.calib_lm_run_resident(
+            self._h, int(maxIters), lam0, lam_min, lam_max, err_min,
+            ctypes.cast(ctypes.byref(sse), _lib._d), ctypes.byref(iters)))
+        return sse.value, iters.value
+
+    def download(self):
+        P = np.empty(self.K)
+        self._check(self._L.calib_download_params(self._h, dptr(P)))
+        return P
+
+    def download_trace(self, iters):
+        t = np.empty((iters, 4))
+        self._check(self._L.calib_download_trace(self._h, int(iters), dptr(t)))
+        return t
+
+    def last_run_stats(self):
+        ms = ctypes.c_double()
+        nl = ctypes.c_int64()
+        ne = ctypes.c_int64()
+        self._check(self._L.calib_last_run_stats(self._h, ctypes.cast(ctypes.byref(ms), _lib._d),
+                                                 ctypes.byref(nl), ctypes.byref(ne)))
+        return ms.value, nl.value, ne.value
+
+    def set_profiling(self, on):
+        self._check(self._L.calib_set_profiling(self._h, 1 if on else 0))
+
+    def kernel_time(self, which):
+        ms = ctypes.c_double()
+        n = ctypes.c_int64()
+        self._check(self._L.calib_kernel_time(self._h, int(which), ctypes.cast(ctypes.byref(ms), _lib._d),
+                                              ctypes.byref(n)))
+        return ms.value, n.value
+
+    def flush_l2(self):
+        self._check(self._L.calib_flush_l2(self._h))
+
+    def comm_init(self, nranks, rank, id128: bytes):
+        buf = ctypes.create_string_buffer(id128, 128)
+        self._check(self._L.calib_comm_init(self._h, int(nranks), int(rank), ctypes.cast(buf, ctypes.c_void_p)))
+
+
+def comm_unique_id():
+    buf = ctypes.create_string_buffer(128)
+    rc = _lib.lib().calib_comm_unique_id(ctypes.cast(buf, ctypes.c_void_p))
+    if rc != 0:
+        raise CalibError(rc, (_lib.lib().calib_last_error(None) or b"").decode())
+    return buf.raw
+
+
+def fp64_peak_tflops(device=0):
+    t = ctypes.c_double()
+    rc = _lib.lib().calib_measure_fp64_peak(int(device), ctypes.cast(ctypes.byref(t), _lib._d))
+    if rc != 0:
+        raise CalibError(rc, (_lib.lib().calib_last_error(None) or b"").decode())
+    return t.value
+
+
+class ProjectionJacobian:
+    """Parity face of src/jacobian.py:12-85: compute(P, allModelPoints) -> dense J (2N, L+6M).
+    The product path never builds this matrix; it exists so the reference's Jacobian tests can
+    be run against the CUDA kernels."""
+    _numExtrinsicParamsPerView = 6
+
+    def __init__(self, distortionModel, device=0):
+        self._model = distortion.model_id_of(distortionModel)
+        self._device = device
+
+    def blocks(self, P, allModelPoints):
+        dets = [(np.zeros((len(m), 2)), m) for m in allModelPoints]
+        prob = Problem.from_detections(self._model, dets, self._device)
+        try:
+            _, Jc, Jv = prob.residual_jacobian(P)
+        finally:
+            prob.close()
+        return Jc, Jv
+
+    def compute(self, P, allModelPoints):
+        Jc, Jv = self.blocks(P, allModelPoints)
+        L = Jc.shape[1]
+        M = len(allModelPoints)
+        J = np.zeros((Jc.shape[0], L + 6 * M))
+        J[:, :L] = Jc
+        row = 0
+        for i, m in enumerate(allModelPoints):
+            n = 2 * len(m)
+            J[row:row + n, L + 6 * i:L + 6 * i + 6] = Jv[row:row + n]
+            row += n
+        return J
+
+
+class Calibrator:
+    """Drop-in for the reference's Calibrator on the refinement path (src/calibrate.py:12-283)."""
+    _λinitial = 1e-3
+    _λmin = 1e-10
+    _λmax = 1e+10
+    _Pt_error_min = 1e-12
+
+    def __init__(self, distortionModel, device=0):
+        self._distortionModel = distortionModel
+        self._model = distortion.model_id_of(distortionModel)
+        self._device = device
+        self._jac = None
+        self.lastTrace = None     # (iters,4): E, E', lambda, accepted
+        self.lastIters = 0
+        self.lastDeviceMs = 0.0
+
+    # -- entry points -----------------------------------------------------------------------
+    def calibrate(self, allDetections, maxIters, initial=None):
+        """src/calibrate.py:21-39.  The closed-form initial estimate is outside the GPU path
+        (SURVEY.md section 8f); pass initial=(A, W, k) or subclass estimateCalibrationParameters."""
+        if initial is None:
+            initial = self.estimateCalibrationParameters(allDetections)
+        Ainitial, Winitial, kInitial = initial
+        return self.refineCalibrationParameters(Ainitial, Winitial, kInitial, allDetections,
+                                                maxIters, shouldPrint=True)
+
+    def estimateCalibrationParameters(self, allDetections):
+        raise NotImplementedError(
+            "the linear initial estimate (src/calibrate.py:41-58) is not part of the GPU path; "
+            "use the reference's Calibrator.estimateCalibrationParameters and pass its result")
+
+    def refineCalibrationParameters(self, Ainitial, Winitial, kInitial, allDetections,
+                                    maxIters, shouldPrint=False):
+        """src/calibrate.py:117-171.  Returns (sse, Arefined, Wrefined, kRefined)."""
+        if int(maxIters) <= 0:
+            # the reference returns an unbound Pt_error (src/calibrate.py:171)
+            raise UnboundLocalError("cannot access local variable 'Pt_error' where it is not "
+                                    "associated with a value")
+        ts = time.time()
+        Pt = self._composeParameterVector(Ainitial, Winitial, kInitial)
+        prob = Problem.from_detections(self._model, allDetections, self._device)
+        try:
+            sse, P, iters, trace = prob.lm_run(Pt, int(maxIters), self._λinitial, self._λmin,
+                                               self._λmax, self._Pt_error_min)
+            self.lastDeviceMs = prob.last_run_stats()[0]
+        finally:
+            prob.close()
+        self.lastTrace, self.lastIters = trace, iters
+        if shouldPrint:
+            for it, (E, E1, lam, acc) in enumerate(trace):
+                print(f"\niter {it}: error={min(E1, E):0.3f}, λ={lam:e}")
+            At, Wt, kt = self._decomposeParameterVector(P)
+            print(f"({time.time() - ts:0.3f}s)\nA:\n{At}\nk:\n{kt}")
+        Arefined, Wrefined, kRefined = self._decomposeParameterVector(P)
+        return sse, Arefined, Wrefined, kRefined
+
+    def _initializeJacobian(self):
+        """No symbolic build on this path (src/calibrate.py:173-176 takes ~7 s there)."""
+        if self._jac is None:
+            self._jac = ProjectionJacobian(self._model, self._device)
+
+    def _computeReprojectionError(self, P, allDetections):
+        """src/calibrate.py:178-183"""
+        prob = Problem.from_detections(self._model, allDetections, self._device)
+        try:
+            return prob.cost(P)
+        finally:
+            prob.close()
+
+    def projectAllPoints(self, P, allModelPoints):
+        """src/calibrate.py:190-197"""
+        dets = [(np.zeros((len(m), 2)), m) for m in allModelPoints]
+        prob = Problem.from_detections(self._model, dets, self._device)
+        try:
+            return prob.project(P)
+        finally:
+            prob.close()
+
+    # -- parameter vector layout (host) -----------------------------------------------------
+    def _numDistortion(self):
+        return 5 if self._model == distortion.RADTAN else 4
+
+    def _composeParameterVector(self, A, W, k):
+        """src/calibrate.py:199-229: (K,1) column [α β γ uc vc k..., (ρx ρy ρz tx ty tz) per view]."""
+        A = np.asarray(A, dtype=np.float64)
+        k = list(np.asarray(k, dtype=np.float64).ravel())
+        if len(k) != self._numDistortion():
+            raise ValueError(f"Expected {self._numDistortion()} distortion coefficients, got {len(k)}")
+        vals = [A[0, 0], A[1, 1], A[0, 1], A[0, 2], A[1, 2]] + k
+        for cMw in W:
+            cMw = np.asarray(cMw, dtype=np.float64)
+            mu_shape = cMw.shape
+            if mu_shape != (4, 4):
+                raise ValueError(f"Expected shape (4, 4), got {mu_shape}")
+            vals += list(mu.rotationMatrixToEuler(cMw[:3, :3])) + list(cMw[:3, 3])
+        return mu.col(vals).astype(np.float64)
+
+    def _decomposeParameterVector(self, P):
+        """src/calibrate.py:231-267"""
+        P = np.asarray(P, dtype=np.float64).ravel()
+        nd = self._numDistortion()
+        start = 5 + nd
+        α, β, γ, uc, vc = P[:5]
+        A = np.array([[α, γ, uc], [0, β, vc], [0, 0, 1]])
+        W = []
+        for i in range(start, len(P), 6):
+            ρx, ρy, ρz, tx, ty, tz = P[i:i + 6]
+            W.append(mu.poseFromRT(mu.eulerToRotationMatrix((ρx, ρy, ρz)), (tx, ty, tz)))
+        return A, W, P[5:start]
+
+
+def calibrateCamera(allDetections, distortionType, maxIters, initial=None, device=0):
+    """src/main.py:11-36 with the GPU refinement.  `initial` = (A, W, k) from the (CPU, closed
+    form) initial estimate; ValueError on an unknown distortion type as in the reference."""
+    model = distortion.model_id_of(distortionType)
+    calibrator = Calibrator(model, device)
+    return calibrator.calibrate(allDetections, maxIters, initial=initial)

@@ -1,0 +1,121 @@
+"""Synthetic checkerboard inputs of the named benchmark shapes.  The reference's generators
+(src/dataset.py:59-95, src/virtualcamera.py:33-55, src/checkerboard.py:9-17, src/noise.py:8-18)
+cannot travel to the GPU box, so their procedure is restated here with the same seeded numpy
+RNG calls in the same order: the detections are bit-identical to the reference's (pinned by
+tests/test_synth.py against the detections stored in tests/golden/*.npz)."""
+import numpy as np
+
+from . import distortion
+from . import mathutils as mu
+
+A_SYNTHETIC = np.array([[803.1, 0, 700.5], [0, 803.1, 529.2], [0, 0, 1]], dtype=np.float64)
+K_RADTAN = (-0.25, 0.2, 0.07, -0.03, 0.05)
+K_FISHEYE = (-0.155, -0.02, 0.0, -0.03)
+A_REALISTIC = np.array([[1432.1, 0, 719.2], [0, 1432.1, 564.3], [0, 0, 1]], dtype=np.float64)
+K_REALISTIC = (-0.2674, 0.1716, 1.4287e-05, 0.000177, -0.052701)
+
+
+def checkerboard_corners(numCornersWidth, numCornersHeight, spacing):
+    """src/checkerboard.py:9-17: row-major planar grid, Z = 0."""
+    pts = [(i * spacing, j * spacing, 0) for j in range(numCornersHeight) for i in range(numCornersWidth)]
+    return np.array(pts).reshape(-1, 3)
+
+
+def _camera_pose_in_board(aim, euler, distance):
+    """src/dataset.py:84-95"""
+    perturb = mu.poseFromRT(mu.eulerToRotationMatrix(euler), (0, 0, 0))
+    facing = mu.poseFromRT(mu.eulerToRotationMatrix((180, 0, 0)), aim)
+    back = mu.poseFromRT(np.eye(3), (0, 0, -distance))
+    return facing @ perturb @ back
+
+
+def make_dataset(corners, A, k, model, width, height, numViews, noise_sigma=None,
+                 roll_pitch=(-30, 30), yaw=(-180, 180), dist=(0.5, 1.0), view_seed_base=0):
+    """src/dataset.py:59-82 + src/virtualcamera.py:42-55.  Returns (allDetections, poses) with
+    allDetections = [(sensorPoints (Ni,2), modelPoints (Ni,3))] and poses = board-in-camera 4x4.
+    Uses (and reseeds) numpy's global RNG exactly like the reference: seed = view index."""
+    mdl = (distortion.RadialTangentialModel() if distortion.model_id_of(model) == distortion.RADTAN
+           else distortion.FisheyeModel())
+    n = corners.shape[0]
+    dets, poses = [], []
+    for viewIndex in range(numViews):
+        np.random.seed(view_seed_base + viewIndex)
+        aimIndex = np.random.choice(n)
+        rx = np.random.uniform(*roll_pitch)
+        ry = np.random.uniform(*roll_pitch)
+        rz = np.random.uniform(*yaw)
+        d = np.random.uniform(*dist)
+        cMb = np.linalg.inv(_camera_pose_in_board(corners[aimIndex], (rx, ry, rz), d))
+        poses.append(cMb)
+        cP = mu.transform(cMb, corners)
+        u = mdl.projectWithDistortion(A, cP, k)
+        if noise_sigma is not None:
+            u = u + np.random.normal(0.0, noise_sigma, u.shape)
+        keep = ((u[:, 0] > 0) & (u[:, 0] < width) & (u[:, 1] > 0) & (u[:, 1] < height) & (cP[:, 2] > 0))
+        dets.append((u[keep], corners[keep]))
+    return dets, poses
+
+
+def perturbed_initial(A, k, poses, rs, rel_A=0.01, euler_deg=0.5, trans=0.005, zero_k=True):
+    """Initial guess for sizes where the reference's O(N^2) linear stage cannot run
+    (SURVEY.md section 8d): ground truth perturbed with a fixed RandomState."""
+    A0 = np.array(A, dtype=np.float64)
+    A0[0, 0] *= 1 + rel_A * rs.uniform(-1, 1)
+    A0[1, 1] *= 1 + rel_A * rs.uniform(-1, 1)
+    A0[0, 2] *= 1 + rel_A * rs.uniform(-1, 1)
+    A0[1, 2] *= 1 + rel_A * rs.uniform(-1, 1)
+    k0 = np.zeros(len(k)) if zero_k else np.array(k, dtype=np.float64)
+    W0 = []
+    for cMb in poses:
+        e = np.array(mu.rotationMatrixToEuler(cMb[:3, :3])) + rs.uniform(-euler_deg, euler_deg, 3)
+        t = cMb[:3, 3] + rs.uniform(-trans, trans, 3)
+        W0.append(mu.poseFromRT(mu.eulerToRotationMatrix(e), t))
+    return A0, W0, k0
+
+
+# ---- the named configurations (BASELINE.json "configs") -------------------------------------
+def config(name, scale=1.0):
+    """Returns dict(model, dets, poses, A, k, init=(A0,W0,k0) or None, width, height).
+    cfg1/cfg1n/cfg2/itest use the reference's linear stage for the initial guess (stored in
+    tests/golden); cfg3/cfg4/cfg5 use perturbed ground truth.  `scale` shrinks the number of
+    views of the large configurations for tests."""
+    W, H = 1440, 1080
+    if name in ("cfg1", "cfg1n"):
+        c = checkerboard_corners(9, 6, 0.050)
+        dets, poses = make_dataset(c, A_SYNTHETIC, K_RADTAN, "radtan", W, H, 10,
+                                   0.1 if name == "cfg1n" else None)
+        return dict(model=0, dets=dets, poses=poses, A=A_SYNTHETIC, k=K_RADTAN, init=None)
+    if name == "cfg2":
+        c = checkerboard_corners(9, 6, 0.050)
+        dets, poses = make_dataset(c, A_SYNTHETIC, K_FISHEYE, "fisheye", W, H, 25, 0.1)
+        return dict(model=1, dets=dets, poses=poses, A=A_SYNTHETIC, k=K_FISHEYE, init=None)
+    if name == "itest":
+        c = checkerboard_corners(25, 18, 0.030)
+        dets, poses = make_dataset(c, A_REALISTIC, K_REALISTIC, "radtan", W, H, 15, None)
+        return dict(model=0, dets=dets, poses=poses, A=A_REALISTIC, k=K_REALISTIC, init=None)
+    if name == "cfg3":
+        views = max(2, int(round(1000 * scale)))
+        c = checkerboard_corners(40, 40, 0.72 / 39)
+        dets, poses = make_dataset(c, A_REALISTIC, K_REALISTIC, "radtan", W, H, views, 0.1)
+        init = perturbed_initial(A_REALISTIC, K_REALISTIC, poses, np.random.RandomState(12345))
+        return dict(model=0, dets=dets, poses=poses, A=A_REALISTIC, k=K_REALISTIC, init=init)
+    if name == "cfg5":
+        views = max(2, int(round(10000 * scale)))
+        c = checkerboard_corners(64, 64, 0.72 / 63)
+        dets, poses = make_dataset(c, A_SYNTHETIC, K_FISHEYE, "fisheye", W, H, views, 0.1)
+        init = perturbed_initial(A_SYNTHETIC, K_FISHEYE, poses, np.random.RandomState(12345))
+        return dict(model=1, dets=dets, poses=poses, A=A_SYNTHETIC, k=K_FISHEYE, init=init)
+    raise ValueError("unknown config " + name)
+
+
+def batch_config(n_problems, views=20):
+    """cfg4: independent 20-view calibrations of the 9x6 board; problem j uses view seeds
+    20*j .. 20*j+19 and RandomState(j) for its perturbed initial guess."""
+    c = checkerboard_corners(9, 6, 0.050)
+    out = []
+    for j in range(n_problems):
+        dets, poses = make_dataset(c, A_SYNTHETIC, K_RADTAN, "radtan", 1440, 1080, views, 0.1,
+                                   view_seed_base=views * j)
+        init = perturbed_initial(A_SYNTHETIC, K_RADTAN, poses, np.random.RandomState(j))
+        out.append(dict(model=0, dets=dets, poses=poses, init=init))
+    return out

@@ -1,0 +1,136 @@
+/* libcalib_b200.so -- C-ABI of the B200-native (sm_100a) Levenberg-Marquardt refinement
+ * stage of Zhang's-method camera calibration.
+ *
+ * The reference (pvphan/camera-calibration) is pure Python and has no FFI; the boundary it
+ * offers for this path is the method
+ *     Calibrator.refineCalibrationParameters(A, W, k, allDetections, maxIters, shouldPrint)
+ *         -> (sse, A, W, k)                                   src/calibrate.py:117-171
+ * plus, for parity, ProjectionJacobian.compute (src/jacobian.py:48-85) and
+ * Calibrator.projectAllPoints (src/calibrate.py:190-197).  Each entry point below names the
+ * reference code it replaces.  INTEGRATION.md shows the ctypes stub a maintainer of the
+ * reference would add.
+ *
+ * Conventions
+ *   - plain C, no exceptions or aborts cross the ABI; every call returns 0 on success or a
+ *     negative CALIB_E_* code, and calib_last_error() gives the text;
+ *   - the caller owns every host buffer (C-contiguous float64 / int64, as numpy makes them);
+ *     the library owns the handle and all device memory;
+ *   - calls are synchronous (they return when the handle's stream is idle);
+ *   - a handle is bound to one GPU and is not thread-safe; distinct handles are independent;
+ *   - there is NO CPU fallback: without a CUDA device calib_create fails with CALIB_E_CUDA.
+ *
+ * Parameter vector P (src/calibrate.py:199-229, src/symbolic.py:8-9), L = 10 | 9:
+ *     [alpha, beta, gamma, uc, vc, k...(radtan k1,k2,p1,p2,k3 | fisheye k1..k4),
+ *      (rho_x, rho_y, rho_z [DEGREES], tx, ty, tz) for view 0, ..., view M-1]      K = L + 6M
+ * Points: view-major CSR.  view_offsets[M+1]; model_pts N x 3 (X,Y,Z); sensor_pts N x 2 (u,v).
+ * Jacobian rows: view-major, point order as given, (u,v) interleaved (src/jacobian.py:175-186).
+ */
+#ifndef CALIB_B200_H
+#define CALIB_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CALIB_MODEL_RADTAN 0  /* src/distortion.py:74-108  RadialTangentialModel */
+#define CALIB_MODEL_FISHEYE 1 /* src/distortion.py:194-220 FisheyeModel */
+
+#define CALIB_OK 0
+#define CALIB_E_ARG -1    /* bad argument (NULL, negative size, unknown model) */
+#define CALIB_E_CUDA -2   /* CUDA runtime error or no device */
+#define CALIB_E_STATE -3  /* call not valid in this state (e.g. maxIters <= 0) */
+#define CALIB_E_COMM -4   /* NCCL error / communicator missing */
+
+typedef struct calib_handle calib_t;
+typedef struct calib_batch_handle calib_batch_t;
+
+/* Last error text of a handle (or of the last failed create when h == NULL). */
+const char* calib_last_error(const calib_t* h);
+
+/* Copies the detections to device memory once (they are constant over the LM loop).
+ * Replaces the per-iteration Python lists of src/calibrate.py:138-139,277-282. */
+int calib_create(calib_t** out, int model, int64_t M, const int64_t* view_offsets,
+                 const double* model_pts, const double* sensor_pts, int device_id);
+void calib_destroy(calib_t* h);
+
+int64_t calib_num_params(const calib_t* h);  /* K = L + 6M */
+int64_t calib_num_points(const calib_t* h);  /* N */
+
+/* Tuning: points per warp task of the fused pass (0 = automatic).  Rebuilds the task list. */
+int calib_set_segment(calib_t* h, int points_per_task);
+
+/* Calibrator.projectAllPoints, src/calibrate.py:190-197.  y: N x 2. */
+int calib_project(calib_t* h, const double* P, double* y);
+
+/* Calibrator._computeReprojectionError, src/calibrate.py:178-188. */
+int calib_cost(calib_t* h, const double* P, double* E);
+
+/* Parity/debug: r = measured - projected (2N, src/calibrate.py:151) and the two non-zero
+ * blocks of ProjectionJacobian.compute (src/jacobian.py:76-83): Jc 2N x L, Jv 2N x 6.
+ * Any output may be NULL. */
+int calib_eval_residual_jacobian(calib_t* h, const double* P, double* r, double* Jc, double* Jv);
+
+/* Parity/debug: the blocks of J^T J and J^T r (src/calibrate.py:146,152) as the fused
+ * kernels accumulate them, never forming J: A L x L, B M x L x 6, D M x 6 x 6, g K, E. */
+int calib_eval_normal_equations(calib_t* h, const double* P, double* A, double* B, double* D,
+                                double* g, double* E);
+
+/* One damped step from P without moving: delta (K) solves
+ * (JTJ + lam diag JTJ) delta = JTr  (src/calibrate.py:147,152) by Schur complement. */
+int calib_lm_step(calib_t* h, const double* P, double lam, double* delta);
+
+/* The LM loop of Calibrator.refineCalibrationParameters, src/calibrate.py:141-171, entirely on
+ * the device.  P_inout: K values, refined in place.  lam0/lam_min/lam_max/err_min are the
+ * Calibrator class constants (src/calibrate.py:13-16).  sse_out = cost before the last
+ * executed iteration's step (the reference's stale Pt_error, :155,171).  trace (nullable):
+ * maxIters x 4 doubles, rows (E, E', lambda, accepted) for the executed iterations.
+ * maxIters <= 0 returns CALIB_E_STATE (the reference raises UnboundLocalError). */
+int calib_lm_run(calib_t* h, double* P_inout, int maxIters, double lam0, double lam_min,
+                 double lam_max, double err_min, double* sse_out, int* iters_out, double* trace);
+
+/* Same loop, but P stays on the device between calls: upload / run / download separately so a
+ * caller can time the device part alone (bench.py "value"). */
+int calib_upload_params(calib_t* h, const double* P);
+int calib_lm_run_resident(calib_t* h, int maxIters, double lam0, double lam_min, double lam_max,
+                          double err_min, double* sse_out, int* iters_out);
+int calib_download_params(calib_t* h, double* P);
+int calib_download_trace(calib_t* h, int iters, double* trace);
+
+/* Device time of the last calib_lm_run* (CUDA events on the handle's stream), and the number
+ * of kernels it launched.  Per-kernel timing: calib_set_profiling(h,1) brackets every launch of
+ * the fused passes with events (slower; not for headline numbers). */
+int calib_last_run_stats(const calib_t* h, double* device_ms, int64_t* kernel_launches,
+                         int64_t* jacobian_evals);
+int calib_set_profiling(calib_t* h, int on);
+/* which: 0 = normal-equation pass A (intrinsic block), 1 = pass BD (coupling + view blocks),
+ * 2 = cost pass, 3 = per-view Schur, 4 = solve + back-substitution.  Sums over the last run. */
+int calib_kernel_time(const calib_t* h, int which, double* total_ms, int64_t* launches);
+
+/* Micro-benchmarks used for the roofline denominators (FP64 FMA pipe; device copy). */
+int calib_measure_fp64_peak(int device_id, double* tflops);
+int calib_flush_l2(calib_t* h);
+
+/* Multi-GPU, one process per GPU: views are sharded, every rank holds the L shared parameters
+ * and its own views' extrinsics.  The reduced system (L x L Schur complement, its right-hand
+ * side and the cost) is all-reduced over NCCL each iteration; everything else is local.
+ * id128: the 128-byte ncclUniqueId made by rank 0 and broadcast by the host. */
+int calib_comm_unique_id(void* id128);
+int calib_comm_init(calib_t* h, int nranks, int rank, const void* id128);
+
+/* Batch of independent calibrations (one thread block per problem, whole LM loop in one
+ * launch).  problem_view_offsets[n_problems+1] indexes view_offsets; P is the concatenation
+ * of the problems' parameter vectors; sse/iters have n_problems entries. */
+int calib_batch_create(calib_batch_t** out, int model, int64_t n_problems,
+                       const int64_t* problem_view_offsets, const int64_t* view_offsets,
+                       const double* model_pts, const double* sensor_pts, int device_id);
+void calib_batch_destroy(calib_batch_t* h);
+const char* calib_batch_last_error(const calib_batch_t* h);
+int calib_batch_lm_run(calib_batch_t* h, double* P_inout, int maxIters, double lam0,
+                       double lam_min, double lam_max, double err_min, double* sse_out,
+                       int* iters_out, double* device_ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

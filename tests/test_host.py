@@ -1,0 +1,115 @@
+"""CPU: host-side mirror (parameter layout, angle convention KATs), synthetic inputs bit-identical
+to the reference's, and the C-ABI library exporting every symbol of include/calib_b200.h."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import camera_calibration_b200 as cc
+from camera_calibration_b200 import _lib, distortion, synth
+from camera_calibration_b200 import mathutils as mu
+
+
+def test_library_builds_and_exports_every_declared_symbol():
+    so = _lib.build()
+    assert os.path.exists(so)
+    names = _lib.exported_symbols()
+    assert "calib_lm_run" in names and "calib_create" in names and len(names) >= 25
+    L = ctypes.CDLL(so)
+    for n in names:
+        assert hasattr(L, n), n
+    out = subprocess.run(["nm", "-D", "--defined-only", so], capture_output=True, text=True).stdout
+    for n in names:
+        assert f" T {n}" in out, n
+    # every declared symbol has a ctypes signature in the binding
+    assert set(names) == set(_lib.lib()._signatures)
+
+
+def test_no_cpu_fallback_without_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    c = synth.config("cfg1")
+    with pytest.raises(cc.CalibError):
+        cc.Problem.from_detections(0, c["dets"])
+
+
+def test_euler_known_answers():
+    # tests/test_mathutils.py:112-152 of the reference
+    assert np.allclose(mu.eulerToRotationMatrix((0, 0, 90)), [[0, -1, 0], [1, 0, 0], [0, 0, 1]], atol=1e-12)
+    assert np.allclose(mu.eulerToRotationMatrix((0, 180, 0)), [[-1, 0, 0], [0, 1, 0], [0, 0, -1]], atol=1e-12)
+    assert np.allclose(mu.eulerToRotationMatrix((0, 90, 90)), [[0, -1, 0], [0, 0, 1], [-1, 0, 0]], atol=1e-12)
+    rs = np.random.RandomState(0)
+    for _ in range(20):
+        e = rs.uniform(-89, 89, 3) * np.array([2, 1, 2])
+        R = mu.eulerToRotationMatrix(e)
+        assert np.allclose(R @ R.T, np.eye(3), atol=1e-12)
+        assert np.allclose(mu.eulerToRotationMatrix(mu.rotationMatrixToEuler(R)), R, atol=1e-9)
+    # gimbal cases, tests/test_mathutils.py:275-319
+    for e in ((10, 90, 0), (10, -90, 0)):
+        R = mu.eulerToRotationMatrix(e)
+        assert np.allclose(mu.eulerToRotationMatrix(mu.rotationMatrixToEuler(R)), R, atol=1e-9)
+
+
+@pytest.mark.parametrize("model,k", [(0, (-0.25, 0.2, 0.07, -0.03, 0.05)), (1, (-0.155, -0.02, 0.0, -0.03))])
+def test_parameter_vector_round_trip(model, k):
+    # tests/test_calibrate.py:63-78 of the reference
+    cal = cc.Calibrator(model)
+    A = np.array([[400, 0.3, 320], [0, 410, 240], [0, 0, 1.0]])
+    W = [mu.poseFromRT(mu.eulerToRotationMatrix(e), t) for e, t in
+         (((170, 5, -30), (0.1, 0.2, 1.0)), ((-160, -12, 100), (-0.2, 0.1, 0.7)))]
+    P = cal._composeParameterVector(A, W, k)
+    assert P.shape == (6 * 2 + 5 + len(k), 1)
+    A2, W2, k2 = cal._decomposeParameterVector(P)
+    assert np.allclose(A2, A, atol=1e-9) and np.allclose(k2, k, atol=1e-9)
+    for a, b in zip(W, W2):
+        assert np.allclose(a, b, atol=1e-9)
+    with pytest.raises(ValueError):
+        cal._composeParameterVector(A, W, k[:-1])
+
+
+def test_compose_matches_reference_layout(golden):
+    g = golden("cfg1")
+    cal = cc.Calibrator(distortion.RadialTangentialModel())
+    A, W, k = cal._decomposeParameterVector(g["P0"])
+    P = cal._composeParameterVector(A, W, k).ravel()
+    d = np.abs(P - g["P0"])
+    d = np.minimum(d, np.abs(d - 360))
+    assert d.max() < 1e-9
+
+
+def test_model_selection():
+    assert distortion.model_id_of("radtan") == 0 and distortion.model_id_of("fisheye") == 1
+    assert distortion.model_id_of(distortion.FisheyeModel()) == 1
+    with pytest.raises(ValueError):   # src/main.py:33
+        cc.calibrateCamera([], "pinhole", 10)
+
+    class RefLike:   # the reference's own model objects are duck-typed
+        def getDistortionSymbols(self):
+            return ("k1", "k2", "p1", "p2", "k3")
+    assert distortion.model_id_of(RefLike()) == 0
+
+
+@pytest.mark.parametrize("case", ["cfg1", "cfg1n", "cfg2", "itest"])
+def test_synthetic_inputs_bit_identical_to_reference(golden, case):
+    g = golden(case)
+    c = synth.config(case)
+    offs, mp, sp = cc.flatten_detections(c["dets"])
+    assert np.array_equal(offs, g["view_offsets"])
+    assert np.array_equal(mp, g["model_pts"])
+    assert np.array_equal(sp, g["sensor_pts"])
+    assert np.array_equal(np.array(c["poses"]), g["W_true"])
+    assert np.array_equal(cc.getSensorPoints(c["dets"]), g["sensor_pts"])
+
+
+def test_large_config_shapes():
+    c = synth.config("cfg3", scale=0.01)
+    assert len(c["dets"]) == 10
+    n = [len(s) for s, m in c["dets"]]
+    assert max(n) <= 1600 and min(n) > 100     # ragged views, most corners in view
+    A0, W0, k0 = c["init"]
+    assert len(W0) == 10 and np.all(k0 == 0)
+    b = synth.batch_config(2)
+    assert len(b) == 2 and len(b[0]["dets"]) == 20

@@ -1,0 +1,131 @@
+"""CPU: the oracle (numpy and C restatements) against the golden vectors generated from the
+unmodified reference (oracle/make_golden.py).  This is what pins the oracle."""
+import numpy as np
+import pytest
+
+import calib_oracle as onp
+import oracle_c as oc
+from conftest import jac_relerr, param_relerr
+
+CASES = ["cfg1", "cfg1n", "cfg2", "itest"]
+TOL_J = 1e-10   # north_star: residuals and Jacobian entries to 1e-10 relative
+TOL_P = 1e-8    # north_star: converged parameters to 1e-8 relative
+
+
+@pytest.mark.parametrize("model,name", [(0, "radtan"), (1, "fisheye")])
+def test_kat_vectors(golden, model, name):
+    g = golden("kat")
+    L = onp.num_intrinsics(model)
+    # (a) the reference test's own vector, tests/test_jacobian.py:19-24
+    P, pts = g[name + "_a_P"], g[name + "_a_pts"]
+    offs = np.array([0, len(pts)])
+    for impl in (onp, oc):
+        Jc, Jv = impl.jacobian_blocks(model, P, offs, pts)
+        assert Jc.shape == (2 * len(pts), L) and Jv.shape == (2 * len(pts), 6)
+        assert jac_relerr(Jc, g[name + "_a_Jc"]) < TOL_J
+        assert jac_relerr(Jv, g[name + "_a_Jv"]) < TOL_J
+        assert np.allclose(impl.project(model, P, offs, pts), g[name + "_a_y"], rtol=1e-12, atol=1e-9)
+    # (b) general vector: Z != 0, skew != 0, negative angles
+    P, pts, offs = g[name + "_b_P"], g[name + "_b_pts"], g[name + "_b_offs"]
+    for impl in (onp, oc):
+        Jc, Jv = impl.jacobian_blocks(model, P, offs, pts)
+        assert jac_relerr(Jc, g[name + "_b_Jc"]) < TOL_J
+        assert jac_relerr(Jv, g[name + "_b_Jv"]) < TOL_J
+        assert np.allclose(impl.project(model, P, offs, pts), g[name + "_b_y"], rtol=1e-12, atol=1e-9)
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_residual_and_jacobian_at_initial_guess(golden, case):
+    g = golden(case)
+    m, offs, mp, sp, P0 = int(g["model"]), g["view_offsets"], g["model_pts"], g["sensor_pts"], g["P0"]
+    for impl in (onp, oc):
+        Jc, Jv = impl.jacobian_blocks(m, P0, offs, mp)
+        assert jac_relerr(Jc, g["Jc0"]) < TOL_J
+        assert jac_relerr(Jv, g["Jv0"]) < TOL_J
+        y = impl.project(m, P0, offs, mp)
+        r = (sp - y).reshape(-1)
+        assert np.abs(r - g["r0"]).max() <= 1e-10 * max(1.0, np.abs(g["r0"]).max())
+        E = impl.cost(m, P0, offs, mp, sp)
+        assert abs(E - g["trace"][0, 0]) <= 1e-12 * g["trace"][0, 0]
+
+
+@pytest.mark.parametrize("case", ["cfg1", "cfg1n", "cfg2"])
+def test_normal_equations_and_first_step(golden, case):
+    g = golden(case)
+    m, offs, mp, sp, P0 = int(g["model"]), g["view_offsets"], g["model_pts"], g["sensor_pts"], g["P0"]
+    L = onp.num_intrinsics(m)
+    JTJ, JTr = g["JTJ0"], g["JTr0"]
+    for impl in (onp, oc):
+        A, B, D, gg, E = impl.normal_equations(m, P0, offs, mp, sp)
+        sc = np.abs(JTJ).max()
+        assert np.abs(A - JTJ[:L, :L]).max() < 1e-12 * sc
+        for v in range(len(offs) - 1):
+            c = L + 6 * v
+            assert np.abs(B[v] - JTJ[:L, c:c + 6]).max() < 1e-12 * sc
+            assert np.abs(D[v] - JTJ[c:c + 6, c:c + 6]).max() < 1e-12 * sc
+        assert np.abs(gg - JTr).max() < 1e-12 * np.abs(JTr).max()
+    # first step: the reference's explicit inverse at cond ~5e9 limits agreement
+    d = oc.lm_step(m, A, B, D, gg, 1e-3)
+    assert np.abs(d - g["delta0"]).max() < 1e-6 * np.abs(g["delta0"]).max()
+    d2 = onp.schur_step(A, B, D, gg, 1e-3)
+    assert np.abs(d - d2).max() < 1e-9 * np.abs(d2).max()
+
+
+def _check_trace(tr, gt):
+    """identical (accepted, lambda) sequence up to the first plateau iteration
+    (|E'-E| <= 1e-10 E), where the reference's own decisions are LAPACK rounding noise."""
+    n = min(len(tr), len(gt))
+    plateau = np.where(np.abs(gt[:, 1] - gt[:, 0]) <= 1e-10 * gt[:, 0])[0]
+    stop = min(n, plateau[0]) if len(plateau) else n
+    assert np.array_equal(tr[:stop, 3], gt[:stop, 3])
+    assert np.array_equal(tr[:stop, 2], gt[:stop, 2])
+    big = gt[:stop, 0] > 1e-9   # costs comparable while they are above rounding level
+    assert np.allclose(tr[:stop, 0][big], gt[:stop, 0][big], rtol=1e-6)
+    return stop
+
+
+@pytest.mark.parametrize("case,impl_name", [("cfg1", "dense"), ("cfg1", "c"), ("cfg1n", "dense"),
+                                            ("cfg1n", "c"), ("cfg2", "c"), ("itest", "c")])
+def test_lm_loop_against_reference(golden, case, impl_name):
+    g = golden(case)
+    m, offs, mp, sp, P0 = int(g["model"]), g["view_offsets"], g["model_pts"], g["sensor_pts"], g["P0"]
+    if impl_name == "dense":
+        sse, P, iters, tr = onp.lm_dense(m, P0, offs, mp, sp, int(g["maxIters"]))
+    else:
+        sse, P, iters, tr = oc.lm(m, P0, offs, mp, sp, int(g["maxIters"]))
+    gt = g["trace"]
+    _check_trace(tr, gt)
+    # the explicit inverse at cond ~5e9 makes the plateau steps of the dense variant (and of the
+    # reference itself) noisy at the 1e-8 level in the weakly determined skew; the Cholesky/Schur
+    # solve lands within 1e-10 of the reference's fixed point
+    assert param_relerr(P, g["Pfinal"]) < (1e-6 if (impl_name == "dense" and case == "cfg1n") else TOL_P)
+    if case in ("cfg1", "itest"):   # noise-free: the count is solver independent
+        assert iters == int(g["iters"])
+        assert sse < 1e-12
+    else:
+        assert abs(sse - float(g["sse"])) < 1e-9 * float(g["sse"])
+    if case == "cfg1n" and impl_name == "dense":
+        assert iters == int(g["iters"])   # same explicit-inverse solve -> same plateau walk here
+
+
+def test_sparse_numpy_equals_c(golden):
+    g = golden("cfg1")
+    m, offs, mp, sp, P0 = int(g["model"]), g["view_offsets"], g["model_pts"], g["sensor_pts"], g["P0"]
+    s1, P1, i1, t1 = onp.lm_sparse(m, P0, offs, mp, sp, 100)
+    s2, P2, i2, t2 = oc.lm(m, P0, offs, mp, sp, 100)
+    assert i1 == i2 and np.array_equal(t1[:, 3], t2[:, 3])
+    assert param_relerr(P1, P2) < 1e-9
+
+
+def test_reference_quirks():
+    g_offs = np.array([0, 2])
+    pts = np.array([[0.1, 0.1, 0], [0.1, 0.2, 0]])
+    P = np.array([400, 400, 0, 320, 240, -0.5, 0.2, 0, 0, 0, 180, 0, 0, 0.1, 0.2, 1.0])
+    with pytest.raises(UnboundLocalError):   # maxIters=0, src/calibrate.py:171
+        onp.lm_dense(0, P, g_offs, pts, np.zeros((2, 2)), 0)
+    with pytest.raises(UnboundLocalError):
+        oc.lm(0, P, g_offs, pts, np.zeros((2, 2)), 0)
+    # block sparsity of the dense layout, tests/test_jacobian.py:56-70
+    P2 = np.concatenate([P, [170, 5, 3, 0.1, 0.2, 1.1]])
+    J = onp.dense_jacobian(0, P2, np.array([0, 2, 4]), np.vstack([pts, pts]))
+    assert J.shape == (8, 22) and J[0, 0] != 0 and J[-1, -1] != 0 and J[0, 16] == 0

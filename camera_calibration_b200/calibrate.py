@@ -189,6 +189,9 @@ class Problem:
         buf = ctypes.create_string_buffer(id128, 128)
         self._check(self._L.calib_comm_init(self._h, int(nranks), int(rank), ctypes.cast(buf, ctypes.c_void_p)))
 
+    def comm_share(self, owner):
+        self._check(self._L.calib_comm_share(self._h, owner._h))
+
 
 def comm_unique_id():
     buf = ctypes.create_string_buffer(128)

@@ -42,6 +42,7 @@ struct calib_handle {
     int64_t kcount[5] = {0, 0, 0, 0, 0};
     std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> prof_events;
     ncclComm_t comm = nullptr;
+    bool comm_owned = false;
     int nranks = 1, rank = 0;
     double* l2buf = nullptr;
     size_t l2bytes = 0;
@@ -242,7 +243,7 @@ extern "C" void calib_destroy(calib_t* h) {
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     drop_graph(h);
-    if (h->comm && g_nccl.ok) g_nccl.CommDestroy(h->comm);
+    if (h->comm && h->comm_owned && g_nccl.ok) g_nccl.CommDestroy(h->comm);
     for (auto& pe : h->prof_events) { cudaEventDestroy(pe.second.first); cudaEventDestroy(pe.second.second); }
     free_pool(h->allocs);
     free_pool(h->fixed);
@@ -696,7 +697,8 @@ extern "C" int calib_comm_init(calib_t* h, int nranks, int rank, const void* id1
     if (!id128 || nranks < 1 || rank < 0 || rank >= nranks) return fail(h, CALIB_E_ARG, "calib_comm_init: bad args");
     if (!nccl_load()) return fail(h, CALIB_E_COMM, "libnccl.so.2 not found");
     drop_graph(h);
-    if (h->comm) { g_nccl.CommDestroy(h->comm); h->comm = nullptr; }
+    if (h->comm && h->comm_owned) g_nccl.CommDestroy(h->comm);
+    h->comm = nullptr; h->comm_owned = false;
     h->nranks = nranks; h->rank = rank;
     if (nranks == 1) return CALIB_OK;
     ncclUniqueId id;
@@ -706,6 +708,18 @@ extern "C" int calib_comm_init(calib_t* h, int nranks, int rank, const void* id1
         h->comm = nullptr;
         return fail(h, CALIB_E_COMM, g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "ncclCommInitRank failed");
     }
+    h->comm_owned = true;
+    return CALIB_OK;
+}
+
+extern "C" int calib_comm_share(calib_t* h, const calib_t* owner) {
+    RC(check_handle(h));
+    if (!owner) return fail(h, CALIB_E_ARG, "calib_comm_share: owner is NULL");
+    if (owner->device != h->device) return fail(h, CALIB_E_ARG, "calib_comm_share: handles on different devices");
+    drop_graph(h);
+    if (h->comm && h->comm_owned) g_nccl.CommDestroy(h->comm);
+    h->comm = owner->comm; h->comm_owned = false;
+    h->nranks = owner->nranks; h->rank = owner->rank;
     return CALIB_OK;
 }
 

@@ -117,6 +117,9 @@ int calib_flush_l2(calib_t* h);
  * id128: the 128-byte ncclUniqueId made by rank 0 and broadcast by the host. */
 int calib_comm_unique_id(void* id128);
 int calib_comm_init(calib_t* h, int nranks, int rank, const void* id128);
+/* Borrow the communicator of another handle of this process (it must outlive h): lets a
+ * long-lived communicator serve one calib_create/calib_lm_run/calib_destroy per calibration. */
+int calib_comm_share(calib_t* h, const calib_t* owner);
 
 /* Batch of independent calibrations (one thread block per problem, whole LM loop in one
  * launch).  problem_view_offsets[n_problems+1] indexes view_offsets; P is the concatenation

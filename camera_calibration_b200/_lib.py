@@ -85,6 +85,9 @@ def lib():
         "calib_num_params": (c_i64, [_vp]),
         "calib_num_points": (c_i64, [_vp]),
         "calib_set_segment": (c_int, [_vp, c_int]),
+        "calib_set_loop_mode": (c_int, [_vp, c_int]),
+        "calib_host_alloc": (_vp, [ctypes.c_size_t]),
+        "calib_host_free": (None, [_vp]),
         "calib_project": (c_int, [_vp, _d, _d]),
         "calib_cost": (c_int, [_vp, _d, _d]),
         "calib_eval_residual_jacobian": (c_int, [_vp, _d, _d, _d, _d]),

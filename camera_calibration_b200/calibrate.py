@@ -92,6 +92,10 @@ class Problem:
     def set_segment(self, n):
         self._check(self._L.calib_set_segment(self._h, int(n)))
 
+    def set_loop_mode(self, mode):
+        """0 auto, 1 host-driven iteration graphs, 2 device-driven WHILE graph."""
+        self._check(self._L.calib_set_loop_mode(self._h, int(mode)))
+
     def project(self, P):
         P = self._P(P)
         y = np.empty((self.N, 2))

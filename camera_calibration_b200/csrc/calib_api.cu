@@ -19,19 +19,34 @@ using namespace calib;
 
 static thread_local std::string g_last_error;
 
+template <typename T>
+static cudaError_t dalloc(std::vector<void*>& pool, T** p, size_t count) {
+    void* q = nullptr;
+    cudaError_t e = cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(T));
+    if (e == cudaSuccess) { pool.push_back(q); *p = (T*)q; }
+    return e;
+}
+
+static void free_pool(std::vector<void*>& pool) {
+    for (void* p : pool) cudaFree(p);
+    pool.clear();
+}
+
 struct calib_handle {
-    int model = 0, L = 0, device = 0;
+    int model = 0, L = 0, device = 0, n_sm = 148;
     int64_t M = 0, N = 0, K = 0;
     std::vector<int64_t> view_offsets;
     int seg = 0;
     Dev dev{};
     cudaStream_t stream = nullptr;
-    cudaGraphExec_t graph = nullptr;
+    cudaGraphExec_t graph = nullptr;       // one iteration (host-driven loop)
+    cudaGraphExec_t loop_graph = nullptr;  // WHILE node around the iteration (device-driven loop)
+    int loop_mode = 0;                     // 0 auto, 1 host-driven, 2 device WHILE graph
     LmState* h_state = nullptr;   // pinned
     double* h_pinned = nullptr;   // pinned scratch (kRedN + 8 doubles)
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    std::vector<void*> allocs;    // device allocations tied to the task list
-    std::vector<void*> fixed;     // device allocations for the lifetime of the handle
+    void* arena_fixed = nullptr;  // detections, parameters, per-view tables
+    void* arena_part = nullptr;   // everything that depends on the partition of the points
     int trace_cap = 0;
     int cur = 0;
     std::string err;
@@ -95,65 +110,111 @@ bool nccl_load() {
     g_nccl.ok = g_nccl.GetUniqueId && g_nccl.CommInitRank && g_nccl.AllReduce && g_nccl.CommDestroy;
     return g_nccl.ok;
 }
+
+// Bump allocator over one stream-ordered device allocation (cudaMallocAsync: the pool keeps the
+// memory of a destroyed handle, so creating the next problem does not pay for cudaMalloc again).
+struct Arena {
+    size_t bytes = 0;
+    char* base = nullptr;
+    template <typename T> size_t reserve(size_t count) {
+        const size_t off = bytes;
+        bytes += (std::max<size_t>(count, 1) * sizeof(T) + 255) & ~(size_t)255;
+        return off;
+    }
+    template <typename T> T* at(size_t off) const { return reinterpret_cast<T*>(base + off); }
+};
+
+void pool_keep_memory(int device) {
+    static bool done[64] = {false};
+    if (device < 0 || device >= 64 || done[device]) return;
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+        uint64_t thr = UINT64_MAX;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+    }
+    done[device] = true;
+}
 }  // namespace
-
-template <typename T>
-static cudaError_t dalloc(std::vector<void*>& pool, T** p, size_t count) {
-    void* q = nullptr;
-    cudaError_t e = cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(T));
-    if (e == cudaSuccess) { pool.push_back(q); *p = (T*)q; }
-    return e;
-}
-
-static void free_pool(std::vector<void*>& pool) {
-    for (void* p : pool) cudaFree(p);
-    pool.clear();
-}
 
 static void drop_graph(calib_handle* h) {
     if (h->graph) { cudaGraphExecDestroy(h->graph); h->graph = nullptr; }
+    if (h->loop_graph) { cudaGraphExecDestroy(h->loop_graph); h->loop_graph = nullptr; }
 }
 
-// Splits every view into near-equal tasks of <= seg points and (re)allocates what depends on it.
+// Cuts the N points into n_warps contiguous, near-equal chunks (one per persistent warp) and each
+// chunk into pieces at the view boundaries.
+static void cut_points(const std::vector<int64_t>& offs, int64_t M, int64_t N, int n_warps,
+                       std::vector<Piece>& pieces, std::vector<int>& chunk) {
+    pieces.clear();
+    chunk.assign((size_t)n_warps + 1, 0);
+    int64_t v = 0;
+    for (int k = 0; k < n_warps; ++k) {
+        int64_t s = (int64_t)((__int128)N * k / n_warps), e = (int64_t)((__int128)N * (k + 1) / n_warps);
+        chunk[k] = (int)pieces.size();
+        while (s < e) {
+            while (v < M && offs[v + 1] <= s) ++v;
+            const int64_t cnt = std::min(e, offs[v + 1]) - s;
+            pieces.push_back(Piece{(int)v, (int)s, (int)cnt, 0});
+            s += cnt;
+        }
+    }
+    chunk[n_warps] = (int)pieces.size();
+}
+
+// (Re)builds the partition of the points and everything sized by it.  seg = points per warp
+// (0 = automatic: one chunk per resident warp of the persistent grids).
 static int build_tasks(calib_handle* h, int seg) {
     drop_graph(h);
-    free_pool(h->allocs);
-    if (seg <= 0) {
-        // automatic: about 6 waves of warp tasks over 148 SMs x 8 resident warps
-        const int64_t target = 148 * 8 * 6;
-        int64_t s = (h->N + target - 1) / std::max<int64_t>(target, 1);
-        s = ((s + 31) / 32) * 32;
-        seg = (int)std::min<int64_t>(512, std::max<int64_t>(64, s));
-    }
+    if (h->arena_part) { cudaFreeAsync(h->arena_part, h->stream); h->arena_part = nullptr; }
     h->seg = seg;
-    std::vector<Task> tasks;
-    std::vector<int> off(h->M + 1, 0);
-    for (int64_t v = 0; v < h->M; ++v) {
-        const int64_t s0 = h->view_offsets[v], n = h->view_offsets[v + 1] - s0;
-        const int64_t parts = (n + seg - 1) / seg;
-        int64_t pos = s0;
-        for (int64_t k = 0; k < parts; ++k) {
-            const int64_t cnt = n / parts + (k < n % parts ? 1 : 0);
-            tasks.push_back(Task{(int)v, (int)pos, (int)cnt, 0});
-            pos += cnt;
+    const int64_t N = h->N, M = h->M;
+    int ev_warps, co_warps;
+    if (seg > 0) {
+        ev_warps = co_warps = (int)std::max<int64_t>(1, (N + seg - 1) / seg);
+    } else {
+        const int64_t by_size = std::max<int64_t>(1, (N + 63) / 64);
+        ev_warps = (int)std::min<int64_t>((int64_t)h->n_sm * kBlockWarps, by_size);
+        co_warps = (int)std::min<int64_t>((int64_t)h->n_sm * kBlockWarps * 2, by_size);
+    }
+    std::vector<Piece> evp, cop;
+    std::vector<int> evc, coc, vp((size_t)M + 1, 0);
+    cut_points(h->view_offsets, M, N, ev_warps, evp, evc);
+    cut_points(h->view_offsets, M, N, co_warps, cop, coc);
+    {   // piece range of every view (pieces are in view order)
+        size_t p = 0;
+        for (int64_t v = 0; v < M; ++v) {
+            vp[v] = (int)p;
+            while (p < evp.size() && evp[p].view == v) ++p;
         }
-        off[v + 1] = (int)tasks.size();
+        vp[M] = (int)evp.size();
     }
     Dev& d = h->dev;
-    d.ntasks = (int)tasks.size();
-    d.nblocks = std::max(1, (d.ntasks + kWarpsPerBlock - 1) / kWarpsPerBlock);
-    d.Tpad = ((d.ntasks + 31) / 32) * 32 + 32;
-    Task* dt = nullptr; int* doff = nullptr;
-    CUDA_TRY(h, dalloc(h->allocs, &dt, tasks.size()));
-    CUDA_TRY(h, dalloc(h->allocs, &doff, off.size()));
-    CUDA_TRY(h, cudaMemcpy(dt, tasks.data(), tasks.size() * sizeof(Task), cudaMemcpyHostToDevice));
-    CUDA_TRY(h, cudaMemcpy(doff, off.data(), off.size() * sizeof(int), cudaMemcpyHostToDevice));
-    d.tasks = dt; d.view_task_off = doff;
-    CUDA_TRY(h, dalloc(h->allocs, &d.partA, (size_t)d.nblocks * kNA));
-    CUDA_TRY(h, dalloc(h->allocs, &d.partE, (size_t)d.nblocks));
-    CUDA_TRY(h, dalloc(h->allocs, &d.partC, (size_t)d.nblocks));
-    CUDA_TRY(h, dalloc(h->allocs, &d.partBD, (size_t)kNBD * d.Tpad));
-    CUDA_TRY(h, cudaMemset(d.partBD, 0, (size_t)kNBD * d.Tpad * sizeof(double)));
+    d.ev_warps = ev_warps; d.ev_blocks = (ev_warps + kBlockWarps - 1) / kBlockWarps; d.ev_pieces = (int)evp.size();
+    d.co_warps = co_warps; d.co_blocks = (co_warps + kBlockWarps - 1) / kBlockWarps;
+    d.sc_blocks = (int)std::max<int64_t>(1, std::min<int64_t>((M + kBlockWarps - 1) / kBlockWarps, 2 * h->n_sm));
+    Arena a;
+    const size_t o_evp = a.reserve<Piece>(evp.size()), o_evc = a.reserve<int>(evc.size());
+    const size_t o_vp = a.reserve<int>(vp.size());
+    const size_t o_cop = a.reserve<Piece>(cop.size()), o_coc = a.reserve<int>(coc.size());
+    const size_t meta_bytes = a.bytes;
+    const size_t o_pA = a.reserve<double>((size_t)d.ev_blocks * kNA), o_pE = a.reserve<double>(d.ev_blocks);
+    const size_t o_pBD = a.reserve<double>((size_t)std::max(d.ev_pieces, 1) * kNBD);
+    const size_t o_pW = a.reserve<double>((size_t)d.sc_blocks * kNBD), o_pC = a.reserve<double>(d.co_blocks);
+    CUDA_TRY(h, cudaMallocAsync(&h->arena_part, a.bytes, h->stream));
+    a.base = (char*)h->arena_part;
+    // one upload for the five index tables
+    std::vector<char> meta(meta_bytes, 0);
+    memcpy(meta.data() + o_evp, evp.data(), evp.size() * sizeof(Piece));
+    memcpy(meta.data() + o_evc, evc.data(), evc.size() * sizeof(int));
+    memcpy(meta.data() + o_vp, vp.data(), vp.size() * sizeof(int));
+    memcpy(meta.data() + o_cop, cop.data(), cop.size() * sizeof(Piece));
+    memcpy(meta.data() + o_coc, coc.data(), coc.size() * sizeof(int));
+    CUDA_TRY(h, cudaMemcpyAsync(a.base, meta.data(), meta_bytes, cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));   // meta is a local
+    d.ev_piece = a.at<Piece>(o_evp); d.ev_chunk = a.at<int>(o_evc); d.view_piece = a.at<int>(o_vp);
+    d.co_piece = a.at<Piece>(o_cop); d.co_chunk = a.at<int>(o_coc);
+    d.partA = a.at<double>(o_pA); d.partE = a.at<double>(o_pE); d.partBD = a.at<double>(o_pBD);
+    d.partW = a.at<double>(o_pW); d.partC = a.at<double>(o_pC);
     return CALIB_OK;
 }
 
@@ -197,40 +258,44 @@ extern "C" int calib_create(calib_t** out, int model, int64_t M, const int64_t* 
     auto bail = [&](int rc) { calib_destroy(h); return rc; };
 #define TRY_(call) do { int rc__ = [&]() -> int { CUDA_TRY(h, call); return 0; }(); if (rc__) { g_last_error = h->err; return bail(rc__); } } while (0)
     TRY_(cudaSetDevice(device_id));
+    pool_keep_memory(device_id);
+    TRY_(cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, device_id));
     TRY_(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     TRY_(cudaEventCreate(&h->ev0));
     TRY_(cudaEventCreate(&h->ev1));
-    TRY_(cudaMallocHost((void**)&h->h_state, sizeof(LmState)));
-    TRY_(cudaMallocHost((void**)&h->h_pinned, (kRedN + 8) * sizeof(double)));
+    TRY_(cudaMallocHost((void**)&h->h_state, sizeof(LmState) + (kRedN + 8) * sizeof(double)));
+    h->h_pinned = reinterpret_cast<double*>(h->h_state + 1);
     Dev& d = h->dev;
     d.model = model; d.L = h->L; d.M = (int)M; d.N = N; d.K = h->K;
-    d.Mpad = (int)(((M + 31) / 32) * 32);
-    // SoA repack on the host, one upload
     {
-        std::vector<double> soa((size_t)5 * std::max<int64_t>(N, 1));
-        for (int64_t i = 0; i < N; ++i) {
-            soa[i] = model_pts[3 * i]; soa[N + i] = model_pts[3 * i + 1]; soa[2 * N + i] = model_pts[3 * i + 2];
-            soa[3 * N + i] = sensor_pts[2 * i]; soa[4 * N + i] = sensor_pts[2 * i + 1];
+        const size_t n = (size_t)std::max<int64_t>(N, 1);
+        Arena a;
+        const size_t o_soa = a.reserve<double>(5 * n + 64);
+        const size_t o_P = a.reserve<double>((size_t)2 * h->K), o_views = a.reserve<ViewC>((size_t)2 * M);
+        const size_t o_red = a.reserve<double>(kRedN), o_vtab = a.reserve<double>((size_t)M * kVtab);
+        const size_t o_et = a.reserve<double>(8), o_delta = a.reserve<double>((size_t)h->K);
+        const size_t o_st = a.reserve<LmState>(1);
+        const size_t zero_from = o_P, zero_bytes = a.bytes - o_P;
+        const size_t o_aos = a.reserve<double>(5 * n);     // upload staging, AoS as the caller holds it
+        TRY_(cudaMallocAsync(&h->arena_fixed, a.bytes, h->stream));
+        a.base = (char*)h->arena_fixed;
+        double* soa = a.at<double>(o_soa);
+        d.X = soa; d.Y = soa + n; d.Z = soa + 2 * n; d.U = soa + 3 * n; d.V = soa + 4 * n;
+        d.Pbuf = a.at<double>(o_P); d.views = a.at<ViewC>(o_views); d.red = a.at<double>(o_red);
+        d.vtab = a.at<double>(o_vtab); d.etrial = a.at<double>(o_et); d.delta = a.at<double>(o_delta);
+        d.st = a.at<LmState>(o_st);
+        TRY_(cudaMemsetAsync(a.base + zero_from, 0, zero_bytes, h->stream));
+        if (N > 0) {
+            double* aos = a.at<double>(o_aos);
+            TRY_(cudaMemcpyAsync(aos, model_pts, (size_t)N * 3 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+            TRY_(cudaMemcpyAsync(aos + 3 * n, sensor_pts, (size_t)N * 2 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+            const int nb = (int)std::min<int64_t>((N + 255) / 256, (int64_t)h->n_sm * 8);
+            k_repack<<<nb, 256, 0, h->stream>>>(aos, aos + 3 * n, N, soa, soa + n, soa + 2 * n, soa + 3 * n, soa + 4 * n);
+            TRY_(cudaGetLastError());
         }
-        double* pts = nullptr;
-        TRY_(dalloc(h->fixed, &pts, soa.size() + 64));
-        TRY_(cudaMemcpy(pts, soa.data(), soa.size() * sizeof(double), cudaMemcpyHostToDevice));
-        d.X = pts; d.Y = pts + N; d.Z = pts + 2 * N; d.U = pts + 3 * N; d.V = pts + 4 * N;
     }
-    TRY_(dalloc(h->fixed, &d.Pbuf, (size_t)2 * h->K));
-    TRY_(cudaMemset(d.Pbuf, 0, (size_t)2 * h->K * sizeof(double)));
-    TRY_(dalloc(h->fixed, &d.views, (size_t)2 * M));
-    const int nvb = (int)((M + kSchurThreads - 1) / kSchurThreads);
-    TRY_(dalloc(h->fixed, &d.partW, (size_t)nvb * (kSchurThreads / 32) * kNBD));
-    TRY_(dalloc(h->fixed, &d.asum, (size_t)kNA));
-    TRY_(dalloc(h->fixed, &d.red, (size_t)kRedN));
-    TRY_(dalloc(h->fixed, &d.vtab, (size_t)vtab_items(h->L) * d.Mpad));
-    TRY_(dalloc(h->fixed, &d.etrial, (size_t)8));
-    TRY_(dalloc(h->fixed, &d.delta, (size_t)h->K));
-    TRY_(dalloc(h->fixed, &d.st, (size_t)1));
-    TRY_(cudaMemset(d.st, 0, sizeof(LmState)));
 #undef TRY_
-    int rc = build_tasks(h, 0);
+    int rc = build_tasks(h, 0);     // synchronises the stream: the caller's buffers are free again
     if (rc) { g_last_error = h->err; return bail(rc); }
     rc = ensure_trace(h, 128);
     if (rc) { g_last_error = h->err; return bail(rc); }
@@ -245,15 +310,14 @@ extern "C" void calib_destroy(calib_t* h) {
     drop_graph(h);
     if (h->comm && h->comm_owned && g_nccl.ok) g_nccl.CommDestroy(h->comm);
     for (auto& pe : h->prof_events) { cudaEventDestroy(pe.second.first); cudaEventDestroy(pe.second.second); }
-    free_pool(h->allocs);
-    free_pool(h->fixed);
+    if (h->arena_part && h->stream) cudaFreeAsync(h->arena_part, h->stream);
+    if (h->arena_fixed && h->stream) cudaFreeAsync(h->arena_fixed, h->stream);
     if (h->dev.trace) cudaFree(h->dev.trace);
     if (h->l2buf) cudaFree(h->l2buf);
     if (h->h_state) cudaFreeHost(h->h_state);
-    if (h->h_pinned) cudaFreeHost(h->h_pinned);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
-    if (h->stream) cudaStreamDestroy(h->stream);
+    if (h->stream) { cudaStreamSynchronize(h->stream); cudaStreamDestroy(h->stream); }
     delete h;
 }
 
@@ -268,20 +332,36 @@ extern "C" int calib_set_segment(calib_t* h, int points_per_task) {
     return build_tasks(h, points_per_task);
 }
 
+extern "C" int calib_set_loop_mode(calib_t* h, int mode) {
+    if (!h) return fail(nullptr, CALIB_E_ARG, "NULL handle");
+    if (mode < 0 || mode > 2) return fail(h, CALIB_E_ARG, "calib_set_loop_mode: 0 auto, 1 host, 2 device");
+    h->loop_mode = mode;
+    return CALIB_OK;
+}
+
+extern "C" void* calib_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    if (cudaMallocHost(&p, std::max<size_t>(bytes, 1)) != cudaSuccess) {
+        g_last_error = "calib_host_alloc: cudaMallocHost failed";
+        return nullptr;
+    }
+    return p;
+}
+extern "C" void calib_host_free(void* p) { if (p) cudaFreeHost(p); }
+
 // ---- launches ---------------------------------------------------------------------------------
 namespace {
 
-enum { KA = 0, KBD = 1, KCOST = 2, KSCHUR = 3, KSOLVE = 4 };
+enum { KEVAL = 0, KSCHUR = 1, KBACK = 2, KCOST = 3, KSOLVE = 4 };
 
 struct Launcher {
     calib_handle* h;
     bool prof;
     int64_t count = 0;
-    void begin(int which, cudaEvent_t* a, cudaEvent_t* b) {
+    void begin(cudaEvent_t* a, cudaEvent_t* b) {
         if (!prof) return;
         cudaEventCreate(a); cudaEventCreate(b);
         cudaEventRecord(*a, h->stream);
-        (void)which;
     }
     void end(int which, cudaEvent_t a, cudaEvent_t b) {
         if (!prof) return;
@@ -294,34 +374,38 @@ template <int MODEL>
 void enqueue_eval(calib_handle* h, Launcher& ln) {
     const Dev& d = h->dev;
     cudaEvent_t a, b;
-    ln.begin(KA, &a, &b);
-    k_eval_A<MODEL><<<d.nblocks, kEvalThreads, 0, h->stream>>>(d);
-    ln.end(KA, a, b);
-    ln.begin(KBD, &a, &b);
-    k_eval_BD<MODEL><<<d.nblocks, kEvalThreads, 0, h->stream>>>(d);
-    ln.end(KBD, a, b);
-    ln.count += 2;
+    ln.begin(&a, &b);
+    k_eval<MODEL><<<d.ev_blocks, kBlockThreads, 0, h->stream>>>(d);
+    ln.end(KEVAL, a, b);
+    ln.count += 1;
 }
 
 template <int MODEL>
-void enqueue_schur(calib_handle* h, Launcher& ln) {
+void enqueue_schur(calib_handle* h, Launcher& ln, int fuse_solve) {
     const Dev& d = h->dev;
-    const int nvb = (d.M + kSchurThreads - 1) / kSchurThreads;
     cudaEvent_t a, b;
-    ln.begin(KSCHUR, &a, &b);
-    k_schur<MODEL><<<nvb + 1, kSchurThreads, 0, h->stream>>>(d);
+    ln.begin(&a, &b);
+    k_schur<MODEL><<<d.sc_blocks + 1, kBlockThreads, 0, h->stream>>>(d, fuse_solve);
     ln.end(KSCHUR, a, b);
     ln.count += 1;
 }
 
 template <int MODEL>
 void enqueue_solve(calib_handle* h, Launcher& ln) {
-    const Dev& d = h->dev;
-    const int nvb = (d.M + kSchurThreads - 1) / kSchurThreads;
     cudaEvent_t a, b;
-    ln.begin(KSOLVE, &a, &b);
-    k_solve_backsub<MODEL><<<nvb, kSchurThreads, 0, h->stream>>>(d);
+    ln.begin(&a, &b);
+    k_solve<MODEL><<<1, 32, 0, h->stream>>>(h->dev);
     ln.end(KSOLVE, a, b);
+    ln.count += 1;
+}
+
+template <int MODEL>
+void enqueue_backsub(calib_handle* h, Launcher& ln) {
+    const Dev& d = h->dev;
+    cudaEvent_t a, b;
+    ln.begin(&a, &b);
+    k_backsub<MODEL><<<d.sc_blocks, kBlockThreads, 0, h->stream>>>(d);
+    ln.end(KBACK, a, b);
     ln.count += 1;
 }
 
@@ -329,8 +413,9 @@ template <int MODEL>
 void enqueue_cost(calib_handle* h, Launcher& ln, int fuse_accept) {
     const Dev& d = h->dev;
     cudaEvent_t a, b;
-    ln.begin(KCOST, &a, &b);
-    k_cost<MODEL><<<d.nblocks, kEvalThreads, 0, h->stream>>>(d, fuse_accept);
+    ln.begin(&a, &b);
+    if (d.use_cond) k_cost<MODEL, true><<<d.co_blocks, kBlockThreads, 0, h->stream>>>(d, fuse_accept);
+    else k_cost<MODEL, false><<<d.co_blocks, kBlockThreads, 0, h->stream>>>(d, fuse_accept);
     ln.end(KCOST, a, b);
     ln.count += 1;
 }
@@ -340,17 +425,19 @@ template <int MODEL>
 int enqueue_iteration(calib_handle* h, Launcher& ln) {
     const Dev& d = h->dev;
     enqueue_eval<MODEL>(h, ln);
-    enqueue_schur<MODEL>(h, ln);
+    enqueue_schur<MODEL>(h, ln, h->comm ? 0 : 1);
     if (h->comm) {
         if (g_nccl.AllReduce(d.red, d.red, kRedN, ncclDouble, ncclSum, h->comm, h->stream) != ncclSuccess)
             return fail(h, CALIB_E_COMM, "ncclAllReduce(reduced system) failed");
+        enqueue_solve<MODEL>(h, ln);
     }
-    enqueue_solve<MODEL>(h, ln);
+    enqueue_backsub<MODEL>(h, ln);
     enqueue_cost<MODEL>(h, ln, h->comm ? 0 : 1);
     if (h->comm) {
         if (g_nccl.AllReduce(d.etrial, d.etrial, 1, ncclDouble, ncclSum, h->comm, h->stream) != ncclSuccess)
             return fail(h, CALIB_E_COMM, "ncclAllReduce(trial cost) failed");
-        k_accept<<<1, 1, 0, h->stream>>>(d);
+        if (d.use_cond) k_accept<true><<<1, 1, 0, h->stream>>>(d);
+        else k_accept<false><<<1, 1, 0, h->stream>>>(d);
         ln.count += 1;
     }
     return CALIB_OK;
@@ -360,11 +447,13 @@ int enqueue_iteration_any(calib_handle* h, Launcher& ln) {
     return h->model == 0 ? enqueue_iteration<0>(h, ln) : enqueue_iteration<1>(h, ln);
 }
 
-int kernels_per_iteration(const calib_handle* h) { return h->comm ? 6 : 5; }
+int kernels_per_iteration(const calib_handle* h) { return h->comm ? 6 : 4; }
 
+// host-driven loop: one iteration as a graph
 int build_graph(calib_handle* h) {
     if (h->graph) return CALIB_OK;
     cudaGraph_t g = nullptr;
+    h->dev.use_cond = 0;
     CUDA_TRY(h, cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
     Launcher ln{h, false};
     int rc = enqueue_iteration_any(h, ln);
@@ -372,6 +461,42 @@ int build_graph(calib_handle* h) {
     if (rc) { if (g) cudaGraphDestroy(g); return rc; }
     CUDA_TRY(h, e);
     e = cudaGraphInstantiate(&h->graph, g, 0);
+    cudaGraphDestroy(g);
+    CUDA_TRY(h, e);
+    return CALIB_OK;
+}
+
+// device-driven loop: a WHILE conditional node whose body is the iteration; the accept step sets
+// the condition (cudaGraphSetConditional), so a whole refinement is ONE graph launch and the host
+// reads the state back once.
+int build_loop_graph(calib_handle* h) {
+    if (h->loop_graph) return CALIB_OK;
+    cudaGraph_t g = nullptr;
+    CUDA_TRY(h, cudaGraphCreate(&g, 0));
+    cudaGraphConditionalHandle handle;
+    cudaError_t e = cudaGraphConditionalHandleCreate(&handle, g, 1, cudaGraphCondAssignDefault);
+    if (e != cudaSuccess) { cudaGraphDestroy(g); CUDA_TRY(h, e); }
+    cudaGraphNodeParams np = {cudaGraphNodeTypeConditional};
+    np.type = cudaGraphNodeTypeConditional;
+    np.conditional.handle = handle;
+    np.conditional.type = cudaGraphCondTypeWhile;
+    np.conditional.size = 1;
+    cudaGraphNode_t node;
+    e = cudaGraphAddNode(&node, g, nullptr, 0, &np);
+    if (e != cudaSuccess) { cudaGraphDestroy(g); CUDA_TRY(h, e); }
+    cudaGraph_t body = np.conditional.phGraph_out[0];
+    h->dev.cond = handle;
+    h->dev.use_cond = 1;
+    e = cudaStreamBeginCaptureToGraph(h->stream, body, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal);
+    if (e != cudaSuccess) { h->dev.use_cond = 0; cudaGraphDestroy(g); CUDA_TRY(h, e); }
+    Launcher ln{h, false};
+    int rc = enqueue_iteration_any(h, ln);
+    cudaGraph_t got = nullptr;
+    e = cudaStreamEndCapture(h->stream, &got);
+    h->dev.use_cond = 0;
+    if (rc) { cudaGraphDestroy(g); return rc; }
+    if (e != cudaSuccess) { cudaGraphDestroy(g); CUDA_TRY(h, e); }
+    e = cudaGraphInstantiate(&h->loop_graph, g, 0);
     cudaGraphDestroy(g);
     CUDA_TRY(h, e);
     return CALIB_OK;
@@ -448,7 +573,10 @@ extern "C" int calib_lm_run_resident(calib_t* h, int maxIters, double lam0, doub
         return fail(h, CALIB_E_STATE, "calib_lm_run: maxIters <= 0 (the reference raises UnboundLocalError)");
     RC(ensure_trace(h, maxIters));
     const bool prof = h->profiling;
-    if (!prof) RC(build_graph(h));
+    // the device-driven loop needs every node of the body on this GPU; with a communicator the
+    // loop is host-driven unless asked for explicitly
+    const bool device_loop = !prof && (h->loop_mode == 2 || (h->loop_mode == 0 && !h->comm));
+    if (!prof) RC(device_loop ? build_loop_graph(h) : build_graph(h));
     for (auto& pe : h->prof_events) { cudaEventDestroy(pe.second.first); cudaEventDestroy(pe.second.second); }
     h->prof_events.clear();
     for (int i = 0; i < 5; ++i) { h->ktime[i] = 0; h->kcount[i] = 0; }
@@ -458,22 +586,31 @@ extern "C" int calib_lm_run_resident(calib_t* h, int maxIters, double lam0, doub
     Launcher ln{h, prof};
     ln.count = 1;
     const int kpi = kernels_per_iteration(h);
-    int enq = 0;
-    int batch = 2;   // iterations enqueued between two looks at the device state
-    while (enq < maxIters) {
-        const int n = std::min(batch, maxIters - enq);
-        for (int i = 0; i < n; ++i) {
-            if (prof) RC(enqueue_iteration_any(h, ln));
-            else { CUDA_TRY(h, cudaGraphLaunch(h->graph, h->stream)); ln.count += kpi; }
-        }
-        enq += n;
+    if (device_loop) {
+        CUDA_TRY(h, cudaGraphLaunch(h->loop_graph, h->stream));
         CUDA_TRY(h, cudaMemcpyAsync(h->h_state, h->dev.st, sizeof(LmState), cudaMemcpyDeviceToHost, h->stream));
+        CUDA_TRY(h, cudaEventRecord(h->ev1, h->stream));
         RC(sync(h));
-        if (h->h_state->done) break;
-        batch = std::min(batch * 2, 8);
+        // skipped evaluations (after a rejected step) still launch and return at once
+        ln.count += (int64_t)kpi * h->h_state->iter;
+    } else {
+        int enq = 0;
+        int batch = 2;   // iterations enqueued between two looks at the device state
+        while (enq < maxIters) {
+            const int n = std::min(batch, maxIters - enq);
+            for (int i = 0; i < n; ++i) {
+                if (prof) RC(enqueue_iteration_any(h, ln));
+                else { CUDA_TRY(h, cudaGraphLaunch(h->graph, h->stream)); ln.count += kpi; }
+            }
+            enq += n;
+            CUDA_TRY(h, cudaMemcpyAsync(h->h_state, h->dev.st, sizeof(LmState), cudaMemcpyDeviceToHost, h->stream));
+            RC(sync(h));
+            if (h->h_state->done) break;
+            batch = std::min(batch * 2, 16);
+        }
+        CUDA_TRY(h, cudaEventRecord(h->ev1, h->stream));
+        RC(sync(h));
     }
-    CUDA_TRY(h, cudaEventRecord(h->ev1, h->stream));
-    RC(sync(h));
     float ms = 0;
     CUDA_TRY(h, cudaEventElapsedTime(&ms, h->ev0, h->ev1));
     h->last_ms = ms;
@@ -532,7 +669,7 @@ namespace {
 template <int MODEL>
 void launch_debug_point(calib_handle* h, double* y, double* r, double* Jc, double* Jv) {
     const Dev& d = h->dev;
-    k_debug_point<MODEL><<<d.nblocks, kEvalThreads, 0, h->stream>>>(d, y, r, Jc, Jv);
+    k_debug_point<MODEL><<<(d.ev_pieces + kBlockWarps - 1) / kBlockWarps + 1, kBlockThreads, 0, h->stream>>>(d, y, r, Jc, Jv);
 }
 
 int debug_point(calib_handle* h, const double* P, double* y, double* r, double* Jc, double* Jv) {
@@ -561,20 +698,25 @@ int debug_point(calib_handle* h, const double* P, double* y, double* r, double* 
     return rc;
 }
 
-// uploads P, evaluates both passes and the Schur stage with damping lam (red[] valid afterwards)
+// uploads P, evaluates the normal equations and the Schur stage with damping lam (red[] valid
+// afterwards); solve: also the reduced solve and the back-substitution (delta valid afterwards)
 int eval_system(calib_handle* h, const double* P, double lam, bool solve) {
     RC(check_handle(h));
     if (!P) return fail(h, CALIB_E_ARG, "P is NULL");
     h->cur = 0;
+    h->dev.use_cond = 0;
     RC(upload_to(h, P, 0));
     RC(push_state(h, lam, 0, 0, 0, 1));
     RC(make_views(h, 1));
     Launcher ln{h, false};
-    if (h->model == 0) { enqueue_eval<0>(h, ln); enqueue_schur<0>(h, ln); }
-    else { enqueue_eval<1>(h, ln); enqueue_schur<1>(h, ln); }
+    if (h->model == 0) { enqueue_eval<0>(h, ln); enqueue_schur<0>(h, ln, 0); }
+    else { enqueue_eval<1>(h, ln); enqueue_schur<1>(h, ln, 0); }
     if (h->comm && g_nccl.AllReduce(h->dev.red, h->dev.red, kRedN, ncclDouble, ncclSum, h->comm, h->stream) != ncclSuccess)
         return fail(h, CALIB_E_COMM, "ncclAllReduce failed");
-    if (solve) { if (h->model == 0) enqueue_solve<0>(h, ln); else enqueue_solve<1>(h, ln); }
+    if (solve) {
+        if (h->model == 0) { enqueue_solve<0>(h, ln); enqueue_backsub<0>(h, ln); }
+        else { enqueue_solve<1>(h, ln); enqueue_backsub<1>(h, ln); }
+    }
     return sync(h);
 }
 }  // namespace
@@ -592,6 +734,7 @@ extern "C" int calib_cost(calib_t* h, const double* P, double* E) {
     RC(check_handle(h));
     if (!P || !E) return fail(h, CALIB_E_ARG, "calib_cost: NULL argument");
     h->cur = 0;
+    h->dev.use_cond = 0;
     RC(upload_to(h, P, 1));
     RC(push_state(h, 0.0, 0, 0, 0, 1));
     RC(make_views(h, 0));

@@ -1,18 +1,23 @@
 // Schur complement over the views, reduced solve and back-substitution (device side of
-// `np.linalg.inv(JTJ + lam*diagJTJ) @ J.T @ r`, src/calibrate.py:147,152, in block form).
+// `np.linalg.inv(JTJ + lam*diagJTJ) @ J.T @ r`, src/calibrate.py:147,152, in block form):
+//   S = A' - sum_v B_v D_v'^-1 B_v^T,  s = g_c - sum_v B_v D_v'^-1 g_v,   S dc = s   (L x L)
+//   dv = D_v'^-1 (g_v - B_v^T dc)                                         (6 x 6 per view)
+// with A' = A + lam diag(A), D_v' = D_v + lam diag(D_v).
 #pragma once
 #include "calib_kernels.cuh"
 
 namespace calib {
 
-// slot of A(i,j), i <= j, in the pass-A layout; -1 = structurally zero
+// slot of A(i,j), i <= j, in the intrinsic-sweep layout; -1 = structurally zero
 template <int ND>
 __host__ __device__ inline int a_slot(int i, int j) {
     using S = SlotsA<ND>;
     if (j < 5) {
-        const int tab[5][5] = {{0, -1, 1, 2, -1}, {-1, 3, -1, -1, 4}, {1, -1, 3, 4, -1},
-                               {2, -1, 4, 5, -1}, {-1, 4, -1, -1, 5}};
-        return tab[i][j];
+        // moments of (xd, yd, 1): rows/columns alpha, beta, gamma, uc, vc; 4-bit entries (slot + 1)
+        //   {0,-1,1,2,-1}, {-1,3,-1,-1,4}, {1,-1,3,4,-1}, {2,-1,4,5,-1}, {-1,4,-1,-1,5}
+        const int c = i * 5 + j;
+        const unsigned long long t = c < 16 ? 0x3054025004003201ull : 0x600500650ull;
+        return (int)((t >> (4 * (c & 15))) & 15) - 1;
     }
     if (i < 5) {
         const int a = j - 5;
@@ -27,98 +32,184 @@ __host__ __device__ inline int a_slot(int i, int j) {
     return S::kk(i - 5, j - 5);
 }
 
-constexpr int vtab_items(int L) { return 21 + 6 * (L + 1); }
-
+// ---- reduced L x L system: Cholesky solve by one warp, trial shared parameters ------------------
+// Lane i keeps row i of S in registers; the factorisation is right-looking (after column j every
+// lane updates the rest of its row), so the serial chain per column is one reciprocal square root,
+// one multiply and two shuffles.
 template <int MODEL>
-__global__ void __launch_bounds__(kSchurThreads) k_schur(Dev d) {
+__device__ __forceinline__ void solve_reduced(const Dev& d, int lane) {
     using T = ModelTraits<MODEL>;
-    constexpr int L = T::L;
+    constexpr int L = T::L, ND = T::ND;
+    using SA = SlotsA<ND>;
+    LmState* st = d.st;
+    const double lam = st->lam;
+    const int i = lane < L ? lane : L - 1;       // idle lanes mirror the last row (no divergence)
+    double row[L];
+#pragma unroll
+    for (int j = 0; j < L; ++j) {
+        const int lo = i < j ? i : j, hi = i < j ? j : i;
+        const int sl = a_slot<ND>(lo, hi);
+        double a = sl >= 0 ? __ldcg(d.red + kRedA + sl) : 0.0;
+        if (i == j) a = fma(lam, a, a);
+        row[j] = a - __ldcg(d.red + kRedW + tri(L, lo, hi));
+    }
+    double rhs = __ldcg(d.red + kRedA + SA::G + i) - __ldcg(d.red + kRedW + L * (L + 1) / 2 + i);
+    double inv[L];
+#pragma unroll
+    for (int j = 0; j < L; ++j) {
+        const double dj = __shfl_sync(0xffffffffu, row[j], j);
+        const double id = rsqrt(dj);             // dj <= 0 or NaN poisons the step (rejected)
+        inv[j] = id;
+        const double lij = row[j] * id;          // column j of the factor (rows >= j meaningful)
+        row[j] = lij;
+#pragma unroll
+        for (int k = j + 1; k < L; ++k) {
+            const double lkj = __shfl_sync(0xffffffffu, lij, k);
+            row[k] = fma(-lij, lkj, row[k]);     // S[i][k] -= L[i][j] L[k][j]
+        }
+    }
+    // L y = s (column oriented): y_j = rhs_j / L_jj, then rhs_i -= L_ij y_j for i > j
+#pragma unroll
+    for (int j = 0; j < L; ++j) {
+        const double yj = __shfl_sync(0xffffffffu, rhs * inv[j], j);
+        if (i == j) rhs = yj;
+        else if (i > j) rhs = fma(-row[j], yj, rhs);
+    }
+    // L^T dc = y: dc_j = y_j / L_jj, then y_i -= L_ji dc_j for i < j (L_ji lives in lane j)
+#pragma unroll
+    for (int j = L - 1; j >= 0; --j) {
+        const double xj = __shfl_sync(0xffffffffu, rhs * inv[j], j);
+        double mine = 0.0;                       // L[j][i]: element i of lane j's row
+#pragma unroll
+        for (int k = 0; k < L; ++k) {
+            const double v = __shfl_sync(0xffffffffu, row[k], j);
+            if (k == i) mine = v;
+        }
+        if (i == j) rhs = xj;
+        else if (i < j) rhs = fma(-mine, xj, rhs);
+    }
+    const int cur = st->cur;
+    if (lane < L) {
+        d.delta[lane] = rhs;
+        d.Pbuf[(long long)(cur ^ 1) * d.K + lane] = d.Pbuf[(long long)cur * d.K + lane] + rhs;
+    }
+    if (lane == 0) st->E_cur = __ldcg(d.red + kRedE);
+}
+
+// ---- per-view Schur stage -------------------------------------------------------------------------
+template <int MODEL>
+__global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) {
+    using T = ModelTraits<MODEL>;
+    constexpr int L = T::L, NZ = L + 1, NT = L * (L + 1) / 2, NW = NT + L;
     using S = SlotsBD<L>;
     LmState* st = d.st;
     if (st->done) return;
-    __shared__ double sred[2][kNA];
+    __shared__ double sv[kBlockWarps][kNBD];       // the view's summed piece rows; reused for sums
+    __shared__ double sz[kBlockWarps][NZ * 6];     // Z = L^-1 [B^T | g_v], column-major by c
+    __shared__ double sl[kBlockWarps][24];         // packed lower factor of the view block
     __shared__ int s_last;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int nvb = gridDim.x - 1;
+    const int nvb = d.sc_blocks;
     if ((int)blockIdx.x == nvb) {
-        // the extra block: column sums of the pass-A rows, and the cost
-        const int col = tid & (kNA - 1), rg = tid >> 6;
+        // the extra block: column sums of the intrinsic-sweep rows, and the cost
+        const int col = tid & (kNA - 1), rg = tid >> 6;          // 4 row groups x 64 columns
         double s = 0.0;
-        for (int r = rg; r < d.nblocks; r += 2) s += d.partA[(long long)r * kNA + col];
-        sred[rg][col] = s;
+        for (int r = rg; r < d.ev_blocks; r += 4) s += __ldcg(d.partA + (long long)r * kNA + col);
+        double (*sa)[kNA] = reinterpret_cast<double (*)[kNA]>(&sv[0][0]);
+        sa[rg][col] = s;
         __syncthreads();
-        if (tid < kNA) d.red[kRedA + tid] = sred[0][tid] + sred[1][tid];
-        if (warp == 3) {
-            const double e = warp_sum_array(d.partE, d.nblocks, lane);
+        if (tid < kNA) d.red[kRedA + tid] = (sa[0][tid] + sa[1][tid]) + (sa[2][tid] + sa[3][tid]);
+        if (warp == 7) {
+            const double e = warp_sum_array(d.partE, d.ev_blocks, lane);
             if (lane == 0) {
                 d.red[kRedE] = e;
                 if (st->need_eval) st->n_eval += 1;
             }
         }
     } else {
-        const int v = blockIdx.x * kSchurThreads + tid;
-        double wv[kNBD];
+        // which entries of W this lane accumulates: e = lane + 32 k  ->  (p, c), c in [p, L]
+        int ep[3], ec[3];
 #pragma unroll
-        for (int i = 0; i < kNBD; ++i) wv[i] = 0.0;
-        if (v < d.M) {
-            const int t0 = d.view_task_off[v], t1 = d.view_task_off[v + 1];
-            const double lam = st->lam;
+        for (int k = 0; k < 3; ++k) {
+            int e = lane + 32 * k;
+            ep[k] = -1; ec[k] = 0;
+            if (e < NT) {
+                int p = 0;
+                while (e >= L - p) { e -= L - p; ++p; }
+                ep[k] = p; ec[k] = p + e;
+            } else if (e < NW) {
+                ep[k] = e - NT; ec[k] = L;
+            }
+        }
+        double wacc[3] = {0.0, 0.0, 0.0};
+        const double lam = st->lam;
+        for (int v = blockIdx.x * kBlockWarps + warp; v < d.M; v += nvb * kBlockWarps) {
+            const int r0 = d.view_piece[v], r1 = d.view_piece[v + 1];
+            double s0 = 0.0, s1 = 0.0, s2 = 0.0;
+            for (int r = r0; r < r1; ++r) {
+                const double* row = d.partBD + (long long)r * kNBD;
+                s0 += __ldcg(row + lane); s1 += __ldcg(row + lane + 32); s2 += __ldcg(row + lane + 64);
+            }
+            __syncwarp();
+            sv[warp][lane] = s0; sv[warp][lane + 32] = s1; sv[warp][lane + 64] = s2;
+            __syncwarp();
+            // D' = D + lam diag(D), lower Cholesky, every lane redundantly (registers)
             double Lc[36];
 #pragma unroll
             for (int a = 0; a < 6; ++a)
 #pragma unroll
                 for (int b = a; b < 6; ++b) {
-                    const double* src = d.partBD + (long long)S::dd(a, b) * d.Tpad;
-                    double s = 0.0;
-                    for (int t = t0; t < t1; ++t) s += src[t];
-                    Lc[b * 6 + a] = (a == b) ? fma(lam, s, s) : s;   // D + lam diag(D)
+                    const double s = sv[warp][S::dd(a, b)];
+                    Lc[b * 6 + a] = (a == b) ? fma(lam, s, s) : s;
                 }
-            chol_inplace<6>(Lc);
             double id[6];
+            chol_inplace<6>(Lc, id);
+            double* vt = d.vtab + (long long)v * kVtab;
+            if (lane == 0) {
 #pragma unroll
-            for (int a = 0; a < 6; ++a) {
-                id[a] = 1.0 / Lc[a * 6 + a];
+                for (int a = 0; a < 6; ++a)
 #pragma unroll
-                for (int b = 0; b <= a; ++b) d.vtab[(long long)(a * (a + 1) / 2 + b) * d.Mpad + v] = Lc[a * 6 + b];
+                    for (int b = 0; b <= a; ++b) sl[warp][a * (a + 1) / 2 + b] = (a == b) ? id[a] : Lc[a * 6 + b];
             }
-            double z[L + 1][6];
-#pragma unroll
-            for (int c = 0; c <= L; ++c) {
-                // forward substitution L z = column c of [B^T | g_v]
+            // forward substitution, lane c <= L solves L z = column c of [B^T | g_v]
+            if (lane < NZ) {
+                double z[6];
 #pragma unroll
                 for (int i = 0; i < 6; ++i) {
-                    const int slot = (c < L) ? (S::B + c * 6 + i) : (S::GV + i);
-                    const double* src = d.partBD + (long long)slot * d.Tpad;
-                    double s = 0.0;
-                    for (int t = t0; t < t1; ++t) s += src[t];
+                    double s = sv[warp][(lane < L) ? (S::B + lane * 6 + i) : (S::GV + i)];
 #pragma unroll
-                    for (int k = 0; k < i; ++k) s -= Lc[i * 6 + k] * z[c][k];
-                    z[c][i] = s * id[i];
-                    d.vtab[(long long)(21 + c * 6 + i) * d.Mpad + v] = z[c][i];
+                    for (int k = 0; k < i; ++k) s = fma(-Lc[i * 6 + k], z[k], s);
+                    z[i] = s * id[i];
+                    sz[warp][lane * 6 + i] = z[i];
                 }
             }
+            __syncwarp();
+            if (lane < 21) vt[lane] = sl[warp][lane];     // strictly-lower factor, 1/diagonal on the diagonal
+            for (int i = lane; i < NZ * 6; i += 32) vt[21 + i] = sz[warp][i];
             // W = Z^T Z (upper triangle) and w = Z^T z_g
 #pragma unroll
-            for (int p = 0; p < L; ++p) {
-#pragma unroll
-                for (int c = p; c < L; ++c) {
+            for (int k = 0; k < 3; ++k) {
+                if (ep[k] >= 0) {
+                    const double* zp = &sz[warp][ep[k] * 6];
+                    const double* zc = &sz[warp][ec[k] * 6];
                     double s = 0.0;
 #pragma unroll
-                    for (int i = 0; i < 6; ++i) s = fma(z[p][i], z[c][i], s);
-                    wv[tri(L, p, c)] = s;
+                    for (int i = 0; i < 6; ++i) s = fma(zp[i], zc[i], s);
+                    wacc[k] += s;
                 }
-                double s = 0.0;
-#pragma unroll
-                for (int i = 0; i < 6; ++i) s = fma(z[p][i], z[L][i], s);
-                wv[L * (L + 1) / 2 + p] = s;
             }
         }
-        warp_reduce_scatter<kNBD>(wv, lane);
-        double* dst = d.partW + (long long)(blockIdx.x * (kSchurThreads / 32) + warp) * kNBD;
+        __syncwarp();
+        sv[warp][lane] = wacc[0]; sv[warp][lane + 32] = wacc[1]; sv[warp][lane + 64] = wacc[2];
+        __syncthreads();
+        if (tid < kNBD) {
+            double s = sv[0][tid];
 #pragma unroll
-        for (int j = 0; j < kNBD / 32; ++j) dst[lane * (kNBD / 32) + j] = wv[j];
+            for (int k = 1; k < kBlockWarps; ++k) s += sv[k][tid];
+            d.partW[(long long)blockIdx.x * kNBD + tid] = s;
+        }
     }
-    // last block to finish sums the per-warp W rows in a fixed order
+    // the last block to finish sums the block rows of W in a fixed order
     __threadfence();
     __syncthreads();
     if (tid == 0) {
@@ -128,104 +219,96 @@ __global__ void __launch_bounds__(kSchurThreads) k_schur(Dev d) {
     __syncthreads();
     if (!s_last) return;
     __threadfence();
+    {   // rows r = warp, warp + 8, ...; three columns per lane; then the eight warps in order
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0;
+#pragma unroll 4
+        for (int r = warp; r < nvb; r += kBlockWarps) {
+            const double* row = d.partW + (long long)r * kNBD;
+            s0 += __ldcg(row + lane); s1 += __ldcg(row + lane + 32); s2 += __ldcg(row + lane + 64);
+        }
+        sv[warp][lane] = s0; sv[warp][lane + 32] = s1; sv[warp][lane + 64] = s2;
+    }
+    __syncthreads();
     if (tid < kNBD) {
-        const int nrows = nvb * (kSchurThreads / 32);
-        double s = 0.0;
-        for (int r = 0; r < nrows; ++r) s += d.partW[(long long)r * kNBD + tid];
+        double s = sv[0][tid];
+#pragma unroll
+        for (int k = 1; k < kBlockWarps; ++k) s += sv[k][tid];
         d.red[kRedW + tid] = s;
     }
     if (tid == 0) st->cnt_schur = 0;
+    if (fuse_solve) {
+        __threadfence();
+        __syncthreads();
+        if (warp == 0) solve_reduced<MODEL>(d, lane);
+    }
 }
 
+// reduced solve as its own launch (after the all-reduce when the views are sharded)
 template <int MODEL>
-__global__ void __launch_bounds__(kSchurThreads) k_solve_backsub(Dev d) {
+__global__ void k_solve(Dev d) {
+    if (d.st->done) return;
+    solve_reduced<MODEL>(d, threadIdx.x);
+}
+
+// ---- back-substitution, trial parameters and trial view constants: one warp per view -------------
+template <int MODEL>
+__global__ void __launch_bounds__(kBlockThreads) k_backsub(Dev d) {
     using T = ModelTraits<MODEL>;
-    constexpr int L = T::L, ND = T::ND;
-    using SA = SlotsA<ND>;
+    constexpr int L = T::L;
     LmState* st = d.st;
     if (st->done) return;
-    __shared__ double Sm[L * L];
-    __shared__ double dc[L];
-    const int tid = threadIdx.x;
-    const double lam = st->lam;
+    __shared__ double srow[kBlockWarps][kVtab];
+    __shared__ double sx[kBlockWarps][8];
+    __shared__ double sdc[16];
+    __shared__ __align__(16) ViewC sview[kBlockWarps];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int cur = st->cur;
     const double* P = d.Pbuf + (long long)cur * d.K;
     double* Pt = d.Pbuf + (long long)(cur ^ 1) * d.K;
-    if (tid < L * L) {
-        const int i = tid / L, j = tid % L;
-        const int lo = i < j ? i : j, hi = i < j ? j : i;
-        const int sl = a_slot<ND>(lo, hi);
-        double a = sl >= 0 ? d.red[kRedA + sl] : 0.0;
-        if (i == j) a = fma(lam, a, a);
-        Sm[tid] = a - d.red[kRedW + tri(L, lo, hi)];
-    }
-    if (tid >= 128 - L) {
-        const int i = tid - (128 - L);
-        dc[i] = d.red[kRedA + SA::G + i] - d.red[kRedW + L * (L + 1) / 2 + i];
-    }
+    if (tid < L) sdc[tid] = d.delta[tid];
     __syncthreads();
-    if (tid == 0) {
-        // lower Cholesky of S and the two triangular solves, serial (L <= 10)
-        for (int j = 0; j < L; ++j) {
-            double dd = Sm[j * L + j];
-            for (int k = 0; k < j; ++k) dd -= Sm[j * L + k] * Sm[j * L + k];
-            dd = dd > 0.0 ? sqrt(dd) : __longlong_as_double(0x7ff8000000000000LL);
-            Sm[j * L + j] = dd;
-            const double id = 1.0 / dd;
-            for (int i = j + 1; i < L; ++i) {
-                double s = Sm[i * L + j];
-                for (int k = 0; k < j; ++k) s -= Sm[i * L + k] * Sm[j * L + k];
-                Sm[i * L + j] = s * id;
+    for (int v = blockIdx.x * kBlockWarps + warp; v < d.M; v += gridDim.x * kBlockWarps) {
+        const double* vt = d.vtab + (long long)v * kVtab;
+        __syncwarp();
+        srow[warp][lane] = vt[lane];
+        srow[warp][lane + 32] = vt[lane + 32];
+        if (lane + 64 < kVtab) srow[warp][lane + 64] = vt[lane + 64];
+        __syncwarp();
+        const double* Lc = &srow[warp][0];          // packed lower factor
+        const double* Zm = &srow[warp][21];         // Z columns, 6 each
+        if (lane < 6) {
+            double s = Zm[L * 6 + lane];
+#pragma unroll
+            for (int p = 0; p < L; ++p) s = fma(-Zm[p * 6 + lane], sdc[p], s);
+            sx[warp][lane] = s;
+        }
+        __syncwarp();
+        if (lane == 0) {
+            double x[6];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) x[i] = sx[warp][i];
+#pragma unroll
+            for (int i = 5; i >= 0; --i) {
+                double s = x[i];
+#pragma unroll
+                for (int k = i + 1; k < 6; ++k) s = fma(-Lc[k * (k + 1) / 2 + i], x[k], s);
+                x[i] = s * Lc[i * (i + 1) / 2 + i];      // the diagonal slot holds 1 / L_ii
             }
+            double e[6];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) {
+                const long long idx = L + 6ll * v + i;
+                e[i] = P[idx] + x[i];
+                Pt[idx] = e[i];
+                d.delta[idx] = x[i];
+            }
+            make_view(e, sview[warp]);
         }
-        for (int i = 0; i < L; ++i) {
-            double s = dc[i];
-            for (int k = 0; k < i; ++k) s -= Sm[i * L + k] * dc[k];
-            dc[i] = s / Sm[i * L + i];
-        }
-        for (int i = L - 1; i >= 0; --i) {
-            double s = dc[i];
-            for (int k = i + 1; k < L; ++k) s -= Sm[k * L + i] * dc[k];
-            dc[i] = s / Sm[i * L + i];
-        }
-        if (blockIdx.x == 0) st->E_cur = d.red[kRedE];
+        __syncwarp();
+        if (lane < kViewDoubles)
+            reinterpret_cast<double*>(d.views + (long long)(cur ^ 1) * d.M + v)[lane] =
+                reinterpret_cast<const double*>(&sview[warp])[lane];
     }
-    __syncthreads();
-    if (blockIdx.x == 0 && tid < L) {
-        Pt[tid] = P[tid] + dc[tid];
-        d.delta[tid] = dc[tid];
-    }
-    const int v = blockIdx.x * kSchurThreads + tid;
-    if (v >= d.M) return;
-    double x[6];
-#pragma unroll
-    for (int i = 0; i < 6; ++i) {
-        double s = d.vtab[(long long)(21 + L * 6 + i) * d.Mpad + v];
-#pragma unroll
-        for (int p = 0; p < L; ++p) s = fma(-d.vtab[(long long)(21 + p * 6 + i) * d.Mpad + v], dc[p], s);
-        x[i] = s;
-    }
-    double Lc[21];
-#pragma unroll
-    for (int i = 0; i < 21; ++i) Lc[i] = d.vtab[(long long)i * d.Mpad + v];
-#pragma unroll
-    for (int i = 5; i >= 0; --i) {
-        double s = x[i];
-#pragma unroll
-        for (int k = i + 1; k < 6; ++k) s -= Lc[k * (k + 1) / 2 + i] * x[k];
-        x[i] = s / Lc[i * (i + 1) / 2 + i];
-    }
-    double e[6];
-#pragma unroll
-    for (int i = 0; i < 6; ++i) {
-        const long long idx = L + 6ll * v + i;
-        e[i] = P[idx] + x[i];
-        Pt[idx] = e[i];
-        d.delta[idx] = x[i];
-    }
-    ViewC w;
-    make_view(e, w);
-    d.views[(long long)(cur ^ 1) * d.M + v] = w;
 }
 
 // ---- parity / debug kernels (not on the timed path) ------------------------------------------
@@ -236,8 +319,8 @@ __global__ void k_debug_point(Dev d, double* y, double* r, double* Jc, double* J
     constexpr int L = T::L, ND = T::ND;
     const int lane = threadIdx.x & 31;
     const int t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (t >= d.ntasks) return;
-    const Task task = d.tasks[t];
+    if (t >= d.ev_pieces) return;
+    const Piece task = d.ev_piece[t];
     const int cur = d.st->cur;
     const double* P = d.Pbuf + (long long)cur * d.K;
     double c[L];
@@ -246,10 +329,10 @@ __global__ void k_debug_point(Dev d, double* y, double* r, double* Jc, double* J
     const ViewC w = d.views[(long long)cur * d.M + task.view];
     for (int i = lane; i < task.count; i += 32) {
         const long long n = task.start + i;
-        double p[5];
+        Pt p;
         load_point(d, n, p);
         PointOut<MODEL> o;
-        point_eval<MODEL, true, true>(c, w, p[0], p[1], p[2], p[3], p[4], o);
+        point_eval<MODEL, true, true>(c, w, p.X, p.Y, p.Z, p.U, p.V, o);
         if (y) { y[2 * n] = o.u; y[2 * n + 1] = o.v; }
         if (r) { r[2 * n] = o.ru; r[2 * n + 1] = o.rv; }
         if (Jc) {
@@ -267,7 +350,7 @@ __global__ void k_debug_point(Dev d, double* y, double* r, double* Jc, double* J
     }
 }
 
-// Unpacks the pass partials into the reference's block layout: A L x L, B M x L x 6,
+// Unpacks the partials into the reference's block layout: A L x L, B M x L x 6,
 // D M x 6 x 6, g K.  red[] must already hold the column sums (k_schur ran).
 template <int MODEL>
 __global__ void k_debug_unpack(Dev d, double* A, double* B, double* D, double* g) {
@@ -286,10 +369,10 @@ __global__ void k_debug_unpack(Dev d, double* A, double* B, double* D, double* g
         }
     }
     if (v >= d.M) return;
-    const int t0 = d.view_task_off[v], t1 = d.view_task_off[v + 1];
+    const int r0 = d.view_piece[v], r1 = d.view_piece[v + 1];
     auto slot_sum = [&](int slot) {
         double s = 0.0;
-        for (int t = t0; t < t1; ++t) s += d.partBD[(long long)slot * d.Tpad + t];
+        for (int r = r0; r < r1; ++r) s += d.partBD[(long long)r * kNBD + slot];
         return s;
     };
     for (int p = 0; p < L; ++p)
@@ -315,6 +398,15 @@ __global__ void k_fp64_peak(double* out, int iters, double a, double b) {
 
 __global__ void k_fill(double* p, long long n, double v) {
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) p[i] = v;
+}
+
+// AoS (model N x 3, sensor N x 2, as numpy holds them) -> the SoA arrays the sweeps stream
+__global__ void k_repack(const double* __restrict__ model, const double* __restrict__ sensor, long long n,
+                         double* X, double* Y, double* Z, double* U, double* V) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        X[i] = model[3 * i]; Y[i] = model[3 * i + 1]; Z[i] = model[3 * i + 2];
+        U[i] = sensor[2 * i]; V[i] = sensor[2 * i + 1];
+    }
 }
 
 }  // namespace calib

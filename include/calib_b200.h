@@ -27,6 +27,7 @@
  */
 #ifndef CALIB_B200_H
 #define CALIB_B200_H
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -57,8 +58,21 @@ void calib_destroy(calib_t* h);
 int64_t calib_num_params(const calib_t* h);  /* K = L + 6M */
 int64_t calib_num_points(const calib_t* h);  /* N */
 
-/* Tuning: points per warp task of the fused pass (0 = automatic).  Rebuilds the task list. */
+/* Tuning: points per warp of the sweeps (0 = automatic: one contiguous chunk per resident warp
+ * of the persistent grids).  Rebuilds the partition; results change only in summation order. */
 int calib_set_segment(calib_t* h, int points_per_task);
+
+/* How the LM loop (src/calibrate.py:143-168) is driven.  2: one CUDA graph whose WHILE node
+ * repeats the iteration until the device-side accept step clears the condition -- a whole
+ * refinement is one launch and one read-back.  1: the host launches iteration graphs in small
+ * batches and looks at the device state between them.  0 (default): 2 on one GPU, 1 when the
+ * views are sharded (the body then holds NCCL nodes). */
+int calib_set_loop_mode(calib_t* h, int mode);
+
+/* Page-locked host memory for detections / parameters handed to calib_create / calib_lm_run
+ * (optional: any host pointer works, pinned ones copy at full PCIe rate).  NULL on failure. */
+void* calib_host_alloc(size_t bytes);
+void calib_host_free(void* p);
 
 /* Calibrator.projectAllPoints, src/calibrate.py:190-197.  y: N x 2. */
 int calib_project(calib_t* h, const double* P, double* y);
@@ -103,8 +117,9 @@ int calib_download_trace(calib_t* h, int iters, double* trace);
 int calib_last_run_stats(const calib_t* h, double* device_ms, int64_t* kernel_launches,
                          int64_t* jacobian_evals);
 int calib_set_profiling(calib_t* h, int on);
-/* which: 0 = normal-equation pass A (intrinsic block), 1 = pass BD (coupling + view blocks),
- * 2 = cost pass, 3 = per-view Schur, 4 = solve + back-substitution.  Sums over the last run. */
+/* which: 0 = fused evaluation pass (k_eval), 1 = per-view Schur + reduced system (k_schur),
+ * 2 = back-substitution (k_backsub), 3 = cost sweep (k_cost), 4 = reduced solve as its own
+ * launch (sharded views only).  Sums over the last run. */
 int calib_kernel_time(const calib_t* h, int which, double* total_ms, int64_t* launches);
 
 /* Micro-benchmarks used for the roofline denominators (FP64 FMA pipe; device copy). */

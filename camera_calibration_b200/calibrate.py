@@ -19,18 +19,64 @@ from . import mathutils as mu
 from ._lib import CalibError, as_f64, dptr
 
 
-def flatten_detections(allDetections):
-    """list of (sensorPoints (Ni,2), modelPoints (Ni,3)) -> CSR (view_offsets, model, sensor)."""
-    counts = [len(m) for s, m in allDetections]
+def flatten_detections(allDetections, out=None):
+    """list of (sensorPoints (Ni,2), modelPoints (Ni,3)) -> CSR (view_offsets, model, sensor).
+    out = (model (>=N,3), sensor (>=N,2)) float64 buffers to fill (e.g. page-locked ones)."""
+    counts = np.fromiter((len(m) for s, m in allDetections), dtype=np.int64, count=len(allDetections))
     offs = np.zeros(len(counts) + 1, dtype=np.int64)
     np.cumsum(counts, out=offs[1:])
     N = int(offs[-1])
-    model = np.empty((N, 3), dtype=np.float64)
-    sensor = np.empty((N, 2), dtype=np.float64)
-    for i, (s, m) in enumerate(allDetections):
-        model[offs[i]:offs[i + 1]] = np.asarray(m, dtype=np.float64).reshape(-1, 3)
-        sensor[offs[i]:offs[i + 1]] = np.asarray(s, dtype=np.float64).reshape(-1, 2)
+    if out is None:
+        model = np.empty((N, 3), dtype=np.float64)
+        sensor = np.empty((N, 2), dtype=np.float64)
+    else:
+        model, sensor = out[0][:N], out[1][:N]
+    if N:
+        try:
+            np.concatenate([m for s, m in allDetections], axis=0, out=model)
+            np.concatenate([s for s, m in allDetections], axis=0, out=sensor)
+        except (ValueError, TypeError):      # odd shapes / dtypes / lists: the careful way
+            for i, (s, m) in enumerate(allDetections):
+                model[offs[i]:offs[i + 1]] = np.asarray(m, dtype=np.float64).reshape(-1, 3)
+                sensor[offs[i]:offs[i + 1]] = np.asarray(s, dtype=np.float64).reshape(-1, 2)
     return offs, model, sensor
+
+
+class PinnedBuffers:
+    """Grow-only page-locked staging for the detections of one Calibrator (calib_host_alloc)."""
+
+    def __init__(self):
+        self._ptr = None
+        self._cap = 0
+        self.model = self.sensor = None
+
+    def reserve(self, n_points):
+        if n_points <= self._cap:
+            return self.model, self.sensor
+        self.release()
+        L = _lib.lib()
+        cap = max(int(n_points * 1.25), 1024)
+        ptr = L.calib_host_alloc(cap * 5 * 8)
+        if not ptr:
+            raise CalibError(-2, "calib_host_alloc failed")
+        buf = (ctypes.c_double * (cap * 5)).from_address(ptr)
+        flat = np.frombuffer(buf, dtype=np.float64)
+        self._ptr, self._cap = ptr, cap
+        self.model = flat[:3 * cap].reshape(cap, 3)
+        self.sensor = flat[3 * cap:].reshape(cap, 2)
+        return self.model, self.sensor
+
+    def release(self):
+        if self._ptr:
+            self.model = self.sensor = None
+            _lib.lib().calib_host_free(self._ptr)
+            self._ptr, self._cap = None, 0
+
+    def __del__(self):
+        try:
+            self.release()
+        except Exception:
+            pass
 
 
 def getSensorPoints(allDetections):
@@ -261,6 +307,7 @@ class Calibrator:
         self.lastTrace = None     # (iters,4): E, E', lambda, accepted
         self.lastIters = 0
         self.lastDeviceMs = 0.0
+        self._pinned = PinnedBuffers()
 
     # -- entry points -----------------------------------------------------------------------
     def calibrate(self, allDetections, maxIters, initial=None):
@@ -286,7 +333,9 @@ class Calibrator:
                                     "associated with a value")
         ts = time.time()
         Pt = self._composeParameterVector(Ainitial, Winitial, kInitial)
-        prob = Problem.from_detections(self._model, allDetections, self._device)
+        n_points = sum(len(m) for s, m in allDetections)
+        offs, mp, sp = flatten_detections(allDetections, out=self._pinned.reserve(n_points))
+        prob = Problem(self._model, offs, mp, sp, self._device)
         try:
             sse, P, iters, trace = prob.lm_run(Pt, int(maxIters), self._λinitial, self._λmin,
                                                self._λmax, self._Pt_error_min)
@@ -334,14 +383,16 @@ class Calibrator:
         k = list(np.asarray(k, dtype=np.float64).ravel())
         if len(k) != self._numDistortion():
             raise ValueError(f"Expected {self._numDistortion()} distortion coefficients, got {len(k)}")
-        vals = [A[0, 0], A[1, 1], A[0, 1], A[0, 2], A[1, 2]] + k
-        for cMw in W:
-            cMw = np.asarray(cMw, dtype=np.float64)
-            mu_shape = cMw.shape
-            if mu_shape != (4, 4):
-                raise ValueError(f"Expected shape (4, 4), got {mu_shape}")
-            vals += list(mu.rotationMatrixToEuler(cMw[:3, :3])) + list(cMw[:3, 3])
-        return mu.col(vals).astype(np.float64)
+        W = np.asarray(W, dtype=np.float64)
+        if W.ndim != 3 or W.shape[1:] != (4, 4):
+            raise ValueError(f"Expected shape (4, 4), got {W.shape[1:] if W.ndim == 3 else W.shape}")
+        P = np.empty(5 + len(k) + 6 * len(W))
+        P[:5] = A[0, 0], A[1, 1], A[0, 1], A[0, 2], A[1, 2]
+        P[5:5 + len(k)] = k
+        ext = P[5 + len(k):].reshape(-1, 6)
+        ext[:, :3] = mu.rotationMatrixToEulerBatch(W[:, :3, :3])
+        ext[:, 3:] = W[:, :3, 3]
+        return P.reshape(-1, 1)
 
     def _decomposeParameterVector(self, P):
         """src/calibrate.py:231-267"""
@@ -350,11 +401,12 @@ class Calibrator:
         start = 5 + nd
         α, β, γ, uc, vc = P[:5]
         A = np.array([[α, γ, uc], [0, β, vc], [0, 0, 1]])
-        W = []
-        for i in range(start, len(P), 6):
-            ρx, ρy, ρz, tx, ty, tz = P[i:i + 6]
-            W.append(mu.poseFromRT(mu.eulerToRotationMatrix((ρx, ρy, ρz)), (tx, ty, tz)))
-        return A, W, P[5:start]
+        ext = P[start:].reshape(-1, 6)
+        Wall = np.zeros((len(ext), 4, 4))
+        Wall[:, :3, :3] = mu.eulerToRotationMatrixBatch(ext[:, :3])
+        Wall[:, :3, 3] = ext[:, 3:]
+        Wall[:, 3, 3] = 1.0
+        return A, list(Wall), P[5:start]
 
 
 def calibrateCamera(allDetections, distortionType, maxIters, initial=None, device=0):

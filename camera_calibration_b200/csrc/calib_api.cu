@@ -5,6 +5,8 @@
 #include <nccl.h>
 
 #include <algorithm>
+#include <chrono>
+#include <mutex>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -48,6 +50,7 @@ struct calib_handle {
     void* arena_fixed = nullptr;  // detections, parameters, per-view tables
     void* arena_part = nullptr;   // everything that depends on the partition of the points
     int trace_cap = 0;
+    double* trace_own = nullptr;  // only when a run asks for more iterations than the arena holds
     int cur = 0;
     std::string err;
     double last_ms = 0;
@@ -136,6 +139,62 @@ void pool_keep_memory(int device) {
 }
 }  // namespace
 
+// Streams, events and the page-locked state block are expensive to create (cudaMallocHost takes
+// about a millisecond); a destroyed handle parks them here for the next calib_create on that GPU.
+namespace {
+struct DevCtx { int device; cudaStream_t stream; cudaEvent_t ev0, ev1; LmState* h_state; };
+std::mutex g_ctx_mu;
+std::vector<DevCtx> g_ctx_free;
+
+bool debug_timing() {
+    static const bool on = getenv("CALIB_DEBUG_TIMING") != nullptr;
+    return on;
+}
+struct ScopeTimer {
+    const char* what;
+    std::chrono::steady_clock::time_point t0;
+    explicit ScopeTimer(const char* w) : what(w), t0(std::chrono::steady_clock::now()) {}
+    ~ScopeTimer() {
+        if (!debug_timing()) return;
+        const double us = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count();
+        fprintf(stderr, "[calib] %-28s %9.1f us\n", what, us);
+    }
+};
+}  // namespace
+
+static int ctx_acquire(calib_handle* h) {
+    {
+        std::lock_guard<std::mutex> lk(g_ctx_mu);
+        for (size_t i = 0; i < g_ctx_free.size(); ++i)
+            if (g_ctx_free[i].device == h->device) {
+                const DevCtx c = g_ctx_free[i];
+                g_ctx_free.erase(g_ctx_free.begin() + i);
+                h->stream = c.stream; h->ev0 = c.ev0; h->ev1 = c.ev1; h->h_state = c.h_state;
+                h->h_pinned = reinterpret_cast<double*>(h->h_state + 1);
+                return CALIB_OK;
+            }
+    }
+    CUDA_TRY(h, cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    CUDA_TRY(h, cudaEventCreate(&h->ev0));
+    CUDA_TRY(h, cudaEventCreate(&h->ev1));
+    CUDA_TRY(h, cudaMallocHost((void**)&h->h_state, sizeof(LmState) + (kRedN + 8) * sizeof(double)));
+    h->h_pinned = reinterpret_cast<double*>(h->h_state + 1);
+    return CALIB_OK;
+}
+
+static void ctx_release(calib_handle* h) {
+    if (h->stream && h->ev0 && h->ev1 && h->h_state) {
+        std::lock_guard<std::mutex> lk(g_ctx_mu);
+        g_ctx_free.push_back(DevCtx{h->device, h->stream, h->ev0, h->ev1, h->h_state});
+    } else {
+        if (h->h_state) cudaFreeHost(h->h_state);
+        if (h->ev0) cudaEventDestroy(h->ev0);
+        if (h->ev1) cudaEventDestroy(h->ev1);
+        if (h->stream) cudaStreamDestroy(h->stream);
+    }
+    h->stream = nullptr; h->ev0 = h->ev1 = nullptr; h->h_state = nullptr; h->h_pinned = nullptr;
+}
+
 static void drop_graph(calib_handle* h) {
     if (h->graph) { cudaGraphExecDestroy(h->graph); h->graph = nullptr; }
     if (h->loop_graph) { cudaGraphExecDestroy(h->loop_graph); h->loop_graph = nullptr; }
@@ -223,7 +282,8 @@ static int ensure_trace(calib_handle* h, int iters) {
     drop_graph(h);
     double* t = nullptr;
     CUDA_TRY(h, cudaMalloc((void**)&t, (size_t)iters * 4 * sizeof(double)));
-    if (h->dev.trace) cudaFree(h->dev.trace);
+    if (h->trace_own) cudaFree(h->trace_own);
+    h->trace_own = t;
     h->dev.trace = t;
     h->trace_cap = iters;
     return CALIB_OK;
@@ -251,6 +311,7 @@ extern "C" int calib_create(calib_t** out, int model, int64_t M, const int64_t* 
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0)
         return fail(nullptr, CALIB_E_CUDA, "calib_create: no CUDA device (this library has no CPU fallback)");
     if (device_id < 0 || device_id >= ndev) return fail(nullptr, CALIB_E_ARG, "calib_create: bad device_id");
+    ScopeTimer tm_("calib_create");
     calib_handle* h = new calib_handle();
     h->model = model; h->L = model == 0 ? 10 : 9; h->device = device_id;
     h->M = M; h->N = N; h->K = h->L + 6 * M;
@@ -260,11 +321,7 @@ extern "C" int calib_create(calib_t** out, int model, int64_t M, const int64_t* 
     TRY_(cudaSetDevice(device_id));
     pool_keep_memory(device_id);
     TRY_(cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, device_id));
-    TRY_(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
-    TRY_(cudaEventCreate(&h->ev0));
-    TRY_(cudaEventCreate(&h->ev1));
-    TRY_(cudaMallocHost((void**)&h->h_state, sizeof(LmState) + (kRedN + 8) * sizeof(double)));
-    h->h_pinned = reinterpret_cast<double*>(h->h_state + 1);
+    { int rc = ctx_acquire(h); if (rc) { g_last_error = h->err; return bail(rc); } }
     Dev& d = h->dev;
     d.model = model; d.L = h->L; d.M = (int)M; d.N = N; d.K = h->K;
     {
@@ -275,6 +332,8 @@ extern "C" int calib_create(calib_t** out, int model, int64_t M, const int64_t* 
         const size_t o_red = a.reserve<double>(kRedN), o_vtab = a.reserve<double>((size_t)M * kVtab);
         const size_t o_et = a.reserve<double>(8), o_delta = a.reserve<double>((size_t)h->K);
         const size_t o_st = a.reserve<LmState>(1);
+        constexpr int kTraceIters = 256;
+        const size_t o_trace = a.reserve<double>(4 * kTraceIters);
         const size_t zero_from = o_P, zero_bytes = a.bytes - o_P;
         const size_t o_aos = a.reserve<double>(5 * n);     // upload staging, AoS as the caller holds it
         TRY_(cudaMallocAsync(&h->arena_fixed, a.bytes, h->stream));
@@ -284,6 +343,8 @@ extern "C" int calib_create(calib_t** out, int model, int64_t M, const int64_t* 
         d.Pbuf = a.at<double>(o_P); d.views = a.at<ViewC>(o_views); d.red = a.at<double>(o_red);
         d.vtab = a.at<double>(o_vtab); d.etrial = a.at<double>(o_et); d.delta = a.at<double>(o_delta);
         d.st = a.at<LmState>(o_st);
+        d.trace = a.at<double>(o_trace);
+        h->trace_cap = kTraceIters;
         TRY_(cudaMemsetAsync(a.base + zero_from, 0, zero_bytes, h->stream));
         if (N > 0) {
             double* aos = a.at<double>(o_aos);
@@ -297,14 +358,13 @@ extern "C" int calib_create(calib_t** out, int model, int64_t M, const int64_t* 
 #undef TRY_
     int rc = build_tasks(h, 0);     // synchronises the stream: the caller's buffers are free again
     if (rc) { g_last_error = h->err; return bail(rc); }
-    rc = ensure_trace(h, 128);
-    if (rc) { g_last_error = h->err; return bail(rc); }
     *out = h;
     return CALIB_OK;
 }
 
 extern "C" void calib_destroy(calib_t* h) {
     if (!h) return;
+    ScopeTimer tm_("calib_destroy");
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     drop_graph(h);
@@ -312,12 +372,10 @@ extern "C" void calib_destroy(calib_t* h) {
     for (auto& pe : h->prof_events) { cudaEventDestroy(pe.second.first); cudaEventDestroy(pe.second.second); }
     if (h->arena_part && h->stream) cudaFreeAsync(h->arena_part, h->stream);
     if (h->arena_fixed && h->stream) cudaFreeAsync(h->arena_fixed, h->stream);
-    if (h->dev.trace) cudaFree(h->dev.trace);
+    if (h->trace_own) cudaFree(h->trace_own);
     if (h->l2buf) cudaFree(h->l2buf);
-    if (h->h_state) cudaFreeHost(h->h_state);
-    if (h->ev0) cudaEventDestroy(h->ev0);
-    if (h->ev1) cudaEventDestroy(h->ev1);
-    if (h->stream) { cudaStreamSynchronize(h->stream); cudaStreamDestroy(h->stream); }
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    ctx_release(h);
     delete h;
 }
 
@@ -471,6 +529,7 @@ int build_graph(calib_handle* h) {
 // reads the state back once.
 int build_loop_graph(calib_handle* h) {
     if (h->loop_graph) return CALIB_OK;
+    ScopeTimer tm_("build_loop_graph");
     cudaGraph_t g = nullptr;
     CUDA_TRY(h, cudaGraphCreate(&g, 0));
     cudaGraphConditionalHandle handle;
@@ -571,6 +630,7 @@ extern "C" int calib_lm_run_resident(calib_t* h, int maxIters, double lam0, doub
     RC(check_handle(h));
     if (maxIters <= 0)
         return fail(h, CALIB_E_STATE, "calib_lm_run: maxIters <= 0 (the reference raises UnboundLocalError)");
+    ScopeTimer tm_("calib_lm_run_resident");
     RC(ensure_trace(h, maxIters));
     const bool prof = h->profiling;
     // the device-driven loop needs every node of the body on this GPU; with a communicator the

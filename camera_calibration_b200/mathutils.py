@@ -79,3 +79,42 @@ def unhom(vHom):
 def transform(b_M_a, aX):
     """src/mathutils.py:195-208"""
     return unhom((b_M_a @ hom(aX).T).T)
+
+
+# ---- batched forms (same arithmetic, one numpy call for all views) --------------------------
+def eulerToRotationMatrixBatch(eulerDegrees):
+    """(M,3) Euler angles in degrees -> (M,3,3), R = Rz @ Ry @ Rx per view
+    (src/mathutils.py:36-51).  Closed form of the three axis rotations; agrees with the scalar
+    Rodrigues evaluation above to rounding."""
+    e = np.radians(np.asarray(eulerDegrees, dtype=np.float64).reshape(-1, 3))
+    sa, ca = np.sin(e[:, 0]), np.cos(e[:, 0])
+    sb, cb = np.sin(e[:, 1]), np.cos(e[:, 1])
+    sg, cg = np.sin(e[:, 2]), np.cos(e[:, 2])
+    R = np.empty((len(e), 3, 3))
+    R[:, 0, 0] = cg * cb
+    R[:, 0, 1] = cg * sb * sa - sg * ca
+    R[:, 0, 2] = cg * sb * ca + sg * sa
+    R[:, 1, 0] = sg * cb
+    R[:, 1, 1] = sg * sb * sa + cg * ca
+    R[:, 1, 2] = sg * sb * ca - cg * sa
+    R[:, 2, 0] = -sb
+    R[:, 2, 1] = cb * sa
+    R[:, 2, 2] = cb * ca
+    return R
+
+
+def rotationMatrixToEulerBatch(R):
+    """(M,3,3) -> (M,3) degrees, the branches of src/mathutils.py:13-33 applied per view."""
+    R = np.asarray(R, dtype=np.float64).reshape(-1, 3, 3)
+    R31 = R[:, 2, 0]
+    reg = ~(np.isclose(R31, +1) | np.isclose(R31, -1))
+    out = np.empty((len(R), 3))
+    with np.errstate(invalid="ignore", divide="ignore"):
+        th = -np.arcsin(np.clip(R31, -1, 1))
+        c = np.cos(th)
+        psi = np.arctan2(R[:, 2, 1] / c, R[:, 2, 2] / c)
+        phi = np.arctan2(R[:, 1, 0] / c, R[:, 0, 0] / c)
+    out[:, 0], out[:, 1], out[:, 2] = psi, th, phi
+    for i in np.nonzero(~reg)[0]:          # gimbal lock: rare, scalar path
+        out[i] = np.radians(rotationMatrixToEuler(R[i]))
+    return np.degrees(out)

@@ -112,7 +112,7 @@ def lib():
         "calib_batch_destroy": (None, [_vp]),
         "calib_batch_last_error": (ctypes.c_char_p, [_vp]),
         "calib_batch_lm_run": (c_int, [_vp, _d, c_int, c_dbl, c_dbl, c_dbl, c_dbl, _d,
-                                       ctypes.POINTER(c_int), _d]),
+                                       ctypes.POINTER(c_int), _d, _d]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)

@@ -243,6 +243,66 @@ class Problem:
         self._check(self._L.calib_comm_share(self._h, owner._h))
 
 
+class BatchProblem:
+    """A batch of independent calibrations resident on one GPU (calib_batch_t): one thread block
+    per problem, the whole LM loop in one launch.  problems: list of allDetections lists."""
+
+    def __init__(self, model, problems, device=0):
+        self.model = distortion.model_id_of(model)
+        self.L = 10 if self.model == distortion.RADTAN else 9
+        self.n = len(problems)
+        views = [len(p) for p in problems]
+        self.prob_view = np.zeros(self.n + 1, dtype=np.int64)
+        np.cumsum(views, out=self.prob_view[1:])
+        flat = [det for p in problems for det in p]
+        self.view_offsets, mp, sp = flatten_detections(flat)
+        self.total_params = self.L * self.n + 6 * int(self.prob_view[-1])
+        self._L = _lib.lib()
+        self._h = ctypes.c_void_p()
+        i64 = ctypes.POINTER(ctypes.c_int64)
+        rc = self._L.calib_batch_create(ctypes.byref(self._h), self.model, self.n,
+                                        self.prob_view.ctypes.data_as(i64),
+                                        self.view_offsets.ctypes.data_as(i64), dptr(mp), dptr(sp), int(device))
+        if rc != 0:
+            msg = self._L.calib_batch_last_error(None)
+            self._h = None
+            raise CalibError(rc, msg.decode() if msg else "calib_batch_create failed")
+
+    def param_slices(self):
+        """slice of problem p inside the concatenated parameter vector"""
+        starts = self.L * np.arange(self.n + 1) + 6 * self.prob_view
+        return [slice(int(starts[p]), int(starts[p + 1])) for p in range(self.n)]
+
+    def lm_run(self, P0, maxIters, lam0=1e-3, lam_min=1e-10, lam_max=1e10, err_min=1e-12, want_trace=False):
+        """P0: concatenated parameter vectors.  Returns (sse[n], P, iters[n], trace[n,maxIters,4] | None, device_ms)."""
+        P = as_f64(P0).ravel().copy()
+        if P.size != self.total_params:
+            raise ValueError(f"Expected {self.total_params} parameters, got {P.size}")
+        sse = np.zeros(self.n)
+        iters = np.zeros(self.n, dtype=np.int32)
+        trace = np.zeros((self.n, max(int(maxIters), 1), 4)) if want_trace else None
+        ms = ctypes.c_double()
+        rc = self._L.calib_batch_lm_run(self._h, dptr(P), int(maxIters), lam0, lam_min, lam_max, err_min,
+                                        dptr(sse), iters.ctypes.data_as(ctypes.POINTER(ctypes.c_int)),
+                                        dptr(trace) if want_trace else None,
+                                        ctypes.cast(ctypes.byref(ms), _lib._d))
+        if rc != 0:
+            msg = self._L.calib_batch_last_error(self._h)
+            raise CalibError(rc, msg.decode() if msg else "")
+        return sse, P, iters, trace, ms.value
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.calib_batch_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 def comm_unique_id():
     buf = ctypes.create_string_buffer(128)
     rc = _lib.lib().calib_comm_unique_id(ctypes.cast(buf, ctypes.c_void_p))

@@ -927,14 +927,173 @@ extern "C" int calib_comm_share(calib_t* h, const calib_t* owner) {
 }
 
 // ---- batch of independent calibrations (calib_batch.cuh) -------------------------------------------
-struct calib_batch_handle { std::string err; };
-extern "C" int calib_batch_create(calib_batch_t** out, int, int64_t, const int64_t*, const int64_t*,
-                                  const double*, const double*, int) {
-    if (out) *out = nullptr;
-    return fail(nullptr, CALIB_E_STATE, "calib_batch_create: not implemented in this build");
+struct calib_batch_handle {
+    int model = 0, L = 0, device = 0;
+    int64_t n_problems = 0, total_views = 0, N = 0, total_params = 0;
+    BatchDev dev{};
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::vector<void*> allocs;
+    double* trace_dev = nullptr;
+    size_t trace_cap = 0;      // doubles
+    size_t smem_bytes = 0;
+    std::string err;
+};
+
+#define BATCH_TRY(h, call)                                                                    \
+    do {                                                                                      \
+        cudaError_t e__ = (call);                                                             \
+        if (e__ != cudaSuccess) {                                                             \
+            char b__[512];                                                                    \
+            snprintf(b__, sizeof b__, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), \
+                     __FILE__, __LINE__);                                                     \
+            if (h) (h)->err = b__;                                                            \
+            g_last_error = b__;                                                               \
+            return CALIB_E_CUDA;                                                              \
+        }                                                                                     \
+    } while (0)
+
+static int bfail(calib_batch_handle* h, int code, const char* msg) {
+    if (h) h->err = msg;
+    g_last_error = msg;
+    return code;
 }
-extern "C" void calib_batch_destroy(calib_batch_t* h) { delete h; }
-extern "C" const char* calib_batch_last_error(const calib_batch_t* h) { return h ? h->err.c_str() : g_last_error.c_str(); }
-extern "C" int calib_batch_lm_run(calib_batch_t*, double*, int, double, double, double, double, double*, int*, double*) {
-    return fail(nullptr, CALIB_E_STATE, "calib_batch_lm_run: not implemented in this build");
+
+extern "C" void calib_batch_destroy(calib_batch_t* h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    free_pool(h->allocs);
+    if (h->trace_dev) cudaFree(h->trace_dev);
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+extern "C" const char* calib_batch_last_error(const calib_batch_t* h) {
+    return h ? h->err.c_str() : g_last_error.c_str();
+}
+
+extern "C" int calib_batch_create(calib_batch_t** out, int model, int64_t n_problems,
+                                  const int64_t* problem_view_offsets, const int64_t* view_offsets,
+                                  const double* model_pts, const double* sensor_pts, int device_id) {
+    if (!out) return bfail(nullptr, CALIB_E_ARG, "calib_batch_create: out is NULL");
+    *out = nullptr;
+    if (model != CALIB_MODEL_RADTAN && model != CALIB_MODEL_FISHEYE)
+        return bfail(nullptr, CALIB_E_ARG, "calib_batch_create: unknown distortion model");
+    if (n_problems <= 0 || !problem_view_offsets || !view_offsets)
+        return bfail(nullptr, CALIB_E_ARG, "calib_batch_create: need n_problems >= 1 and both offset arrays");
+    if (problem_view_offsets[0] != 0 || view_offsets[0] != 0)
+        return bfail(nullptr, CALIB_E_ARG, "calib_batch_create: offsets must start at 0");
+    const int L = model == 0 ? 10 : 9;
+    int64_t max_views = 0, max_points = 0;
+    for (int64_t p = 0; p < n_problems; ++p) {
+        const int64_t a = problem_view_offsets[p], b = problem_view_offsets[p + 1];
+        if (b <= a) return bfail(nullptr, CALIB_E_ARG, "calib_batch_create: every problem needs >= 1 view");
+        max_views = std::max(max_views, b - a);
+    }
+    const int64_t total_views = problem_view_offsets[n_problems];
+    for (int64_t v = 0; v < total_views; ++v)
+        if (view_offsets[v + 1] < view_offsets[v])
+            return bfail(nullptr, CALIB_E_ARG, "calib_batch_create: view_offsets not non-decreasing");
+    for (int64_t p = 0; p < n_problems; ++p)
+        max_points = std::max(max_points, view_offsets[problem_view_offsets[p + 1]] - view_offsets[problem_view_offsets[p]]);
+    const int64_t N = view_offsets[total_views];
+    if (N > 0 && (!model_pts || !sensor_pts)) return bfail(nullptr, CALIB_E_ARG, "calib_batch_create: NULL points");
+    if (N >= (1ll << 31) - 64) return bfail(nullptr, CALIB_E_ARG, "calib_batch_create: too many points");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0)
+        return bfail(nullptr, CALIB_E_CUDA, "calib_batch_create: no CUDA device (this library has no CPU fallback)");
+    if (device_id < 0 || device_id >= ndev) return bfail(nullptr, CALIB_E_ARG, "calib_batch_create: bad device_id");
+    // shared memory: stage the detections when two blocks per SM still fit, else stream them from L2
+    int stage = 1;
+    BatchSmem lay = batch_smem_layout(L, (int)max_views, (int)max_points, 1);
+    if ((size_t)lay.total * 8 > 110 * 1024) { stage = 0; lay = batch_smem_layout(L, (int)max_views, (int)max_points, 0); }
+    if ((size_t)lay.total * 8 > 220 * 1024)
+        return bfail(nullptr, CALIB_E_ARG, "calib_batch_create: a problem has too many views for the one-block-per-problem "
+                                           "path (about 100); use calib_create for it");
+    calib_batch_handle* h = new calib_batch_handle();
+    h->model = model; h->L = L; h->device = device_id; h->n_problems = n_problems;
+    h->total_views = total_views; h->N = N; h->total_params = (int64_t)L * n_problems + 6 * total_views;
+    h->smem_bytes = (size_t)lay.total * 8;
+    auto bail = [&](int rc) { calib_batch_destroy(h); return rc; };
+#define TRYB_(call) do { int rc__ = [&]() -> int { BATCH_TRY(h, call); return 0; }(); if (rc__) return bail(rc__); } while (0)
+    TRYB_(cudaSetDevice(device_id));
+    TRYB_(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    TRYB_(cudaEventCreate(&h->ev0));
+    TRYB_(cudaEventCreate(&h->ev1));
+    BatchDev& d = h->dev;
+    d.model = model; d.L = L; d.n_problems = (int)n_problems; d.max_views = (int)max_views;
+    d.max_points = (int)max_points; d.stage_points = stage;
+    const size_t n = (size_t)std::max<int64_t>(N, 1);
+    double *soa = nullptr, *aos = nullptr;
+    long long *pv = nullptr, *vo = nullptr;
+    TRYB_(dalloc(h->allocs, &soa, 5 * n + 64));
+    TRYB_(dalloc(h->allocs, &aos, 5 * n));
+    TRYB_(dalloc(h->allocs, &pv, (size_t)n_problems + 1));
+    TRYB_(dalloc(h->allocs, &vo, (size_t)total_views + 1));
+    TRYB_(dalloc(h->allocs, &d.P, (size_t)h->total_params));
+    TRYB_(dalloc(h->allocs, &d.sse, (size_t)n_problems));
+    TRYB_(dalloc(h->allocs, &d.iters, (size_t)n_problems));
+    static_assert(sizeof(long long) == sizeof(int64_t), "int64 layout");
+    TRYB_(cudaMemcpyAsync(pv, problem_view_offsets, ((size_t)n_problems + 1) * 8, cudaMemcpyHostToDevice, h->stream));
+    TRYB_(cudaMemcpyAsync(vo, view_offsets, ((size_t)total_views + 1) * 8, cudaMemcpyHostToDevice, h->stream));
+    if (N > 0) {
+        TRYB_(cudaMemcpyAsync(aos, model_pts, (size_t)N * 3 * 8, cudaMemcpyHostToDevice, h->stream));
+        TRYB_(cudaMemcpyAsync(aos + 3 * n, sensor_pts, (size_t)N * 2 * 8, cudaMemcpyHostToDevice, h->stream));
+        k_repack<<<(int)std::min<int64_t>((N + 255) / 256, 1184), 256, 0, h->stream>>>(aos, aos + 3 * n, N, soa, soa + n,
+                                                                                  soa + 2 * n, soa + 3 * n, soa + 4 * n);
+        TRYB_(cudaGetLastError());
+    }
+    d.prob_view = pv; d.view_off = vo;
+    d.X = soa; d.Y = soa + n; d.Z = soa + 2 * n; d.U = soa + 3 * n; d.V = soa + 4 * n;
+    TRYB_(cudaFuncSetAttribute(k_batch_lm<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_bytes));
+    TRYB_(cudaFuncSetAttribute(k_batch_lm<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_bytes));
+    TRYB_(cudaStreamSynchronize(h->stream));
+#undef TRYB_
+    *out = h;
+    return CALIB_OK;
+}
+
+extern "C" int calib_batch_lm_run(calib_batch_t* h, double* P_inout, int maxIters, double lam0,
+                                  double lam_min, double lam_max, double err_min, double* sse_out,
+                                  int* iters_out, double* trace, double* device_ms) {
+    if (!h) return bfail(nullptr, CALIB_E_ARG, "NULL handle");
+    if (!P_inout) return bfail(h, CALIB_E_ARG, "calib_batch_lm_run: P is NULL");
+    if (maxIters <= 0)
+        return bfail(h, CALIB_E_STATE, "calib_batch_lm_run: maxIters <= 0 (the reference raises UnboundLocalError)");
+    BATCH_TRY(h, cudaSetDevice(h->device));
+    BatchDev& d = h->dev;
+    d.max_iters = maxIters; d.lam0 = lam0; d.lam_min = lam_min; d.lam_max = lam_max; d.err_min = err_min;
+    d.want_trace = trace ? 1 : 0;
+    if (trace) {
+        const size_t need = (size_t)h->n_problems * maxIters * 4;
+        if (need > h->trace_cap) {
+            if (h->trace_dev) cudaFree(h->trace_dev);
+            h->trace_dev = nullptr; h->trace_cap = 0;
+            BATCH_TRY(h, cudaMalloc((void**)&h->trace_dev, need * 8));
+            h->trace_cap = need;
+        }
+        BATCH_TRY(h, cudaMemsetAsync(h->trace_dev, 0, need * 8, h->stream));
+        d.trace = h->trace_dev;
+    }
+    BATCH_TRY(h, cudaMemcpyAsync(d.P, P_inout, (size_t)h->total_params * 8, cudaMemcpyHostToDevice, h->stream));
+    BATCH_TRY(h, cudaEventRecord(h->ev0, h->stream));
+    if (h->model == 0) k_batch_lm<0><<<(int)h->n_problems, kBatchThreads, h->smem_bytes, h->stream>>>(d);
+    else k_batch_lm<1><<<(int)h->n_problems, kBatchThreads, h->smem_bytes, h->stream>>>(d);
+    BATCH_TRY(h, cudaGetLastError());
+    BATCH_TRY(h, cudaEventRecord(h->ev1, h->stream));
+    BATCH_TRY(h, cudaMemcpyAsync(P_inout, d.P, (size_t)h->total_params * 8, cudaMemcpyDeviceToHost, h->stream));
+    if (sse_out) BATCH_TRY(h, cudaMemcpyAsync(sse_out, d.sse, (size_t)h->n_problems * 8, cudaMemcpyDeviceToHost, h->stream));
+    if (iters_out) BATCH_TRY(h, cudaMemcpyAsync(iters_out, d.iters, (size_t)h->n_problems * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    if (trace) BATCH_TRY(h, cudaMemcpyAsync(trace, h->trace_dev, (size_t)h->n_problems * maxIters * 32, cudaMemcpyDeviceToHost, h->stream));
+    BATCH_TRY(h, cudaStreamSynchronize(h->stream));
+    BATCH_TRY(h, cudaGetLastError());
+    if (device_ms) {
+        float ms = 0;
+        BATCH_TRY(h, cudaEventElapsedTime(&ms, h->ev0, h->ev1));
+        *device_ms = ms;
+    }
+    return CALIB_OK;
 }

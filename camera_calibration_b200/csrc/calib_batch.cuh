@@ -1,2 +1,295 @@
-// Batch of independent calibrations: one thread block per problem (filled in below).
+// Batch of independent calibrations (BASELINE config 4: a multi-camera rig sweep): one thread block
+// per problem, the WHOLE LM loop of src/calibrate.py:141-171 inside one kernel launch.  The
+// problem's detections, both parameter vectors, the view constants, every block of the normal
+// equations and the Schur factors live in shared memory; nothing but the final parameters, the
+// cost, the iteration count (and, on request, the trace) goes back to global memory.
+// The per-point math and the accumulation are the same device functions the single-problem
+// kernels use (point_eval, accum_A, accum_BD); the small dense stages are re-mapped for a block:
+// one THREAD per view for the 6x6 Cholesky and forward substitution, one thread per entry of
+// W = sum_v Z_v^T Z_v, one warp for the reduced L x L solve.
 #pragma once
+#include "calib_solve.cuh"
+
+namespace calib {
+
+constexpr int kBatchWarps = 4;
+constexpr int kBatchThreads = kBatchWarps * 32;
+constexpr int kBDStride = kNBD + 1;     // 97: odd stride in doubles -> conflict-free thread-per-view reads
+constexpr int kVtStride = kVtab + 1;    // 89
+
+struct BatchDev {
+    int model, L, n_problems, max_views, max_points, stage_points, max_iters, want_trace;
+    const long long* prob_view;   // n_problems + 1 : first view of problem p
+    const long long* view_off;    // total views + 1 : first point of view v
+    const double *X, *Y, *Z, *U, *V;
+    double* P;                    // concatenated parameter vectors; problem p starts at L p + 6 prob_view[p]
+    double* sse;                  // n_problems
+    int* iters;                   // n_problems
+    double* trace;                // n_problems x max_iters x 4 (if want_trace)
+    double lam0, lam_min, lam_max, err_min;
+};
+
+struct BatchSmem {      // offsets in doubles into the dynamic shared memory
+    int P, views, bd, vt, redA, misc, pts, total;
+};
+
+__host__ __device__ inline BatchSmem batch_smem_layout(int L, int max_views, int max_points, int stage_points) {
+    BatchSmem s;
+    const int K = L + 6 * max_views;
+    int o = 0;
+    s.P = o;     o += 2 * ((K + 1) & ~1);
+    s.views = o; o += 2 * max_views * kViewDoubles;
+    s.bd = o;    o += max_views * kBDStride;
+    s.vt = o;    o += max_views * kVtStride;
+    s.redA = o;  o += kBatchWarps * kNA + kNA + kNBD;     // per-warp A rows, summed A, W
+    s.misc = o;  o += 64;                                  // per-warp costs, dc, scalars
+    o = (o + 1) & ~1;
+    s.pts = o;   o += stage_points ? 5 * max_points : 0;
+    s.total = o;
+    return s;
+}
+
+// Per-view Schur stage by ONE thread: bd = the view's summed (B_v | D_v | g_v) row, vt = out row
+// (packed strictly-lower factor with 1/diagonal on the diagonal, then Z column by column).
+template <int MODEL>
+__device__ __forceinline__ void view_schur_thread(const double* bd, double lam, double* vt) {
+    constexpr int L = ModelTraits<MODEL>::L;
+    using S = SlotsBD<L>;
+    double Lc[36], id[6];
+#pragma unroll
+    for (int a = 0; a < 6; ++a)
+#pragma unroll
+        for (int b = a; b < 6; ++b) {
+            const double s = bd[S::dd(a, b)];
+            Lc[b * 6 + a] = (a == b) ? fma(lam, s, s) : s;
+            if (a != b) Lc[a * 6 + b] = 0.0;
+        }
+    chol_inplace<6>(Lc, id);
+#pragma unroll
+    for (int a = 0; a < 6; ++a)
+#pragma unroll
+        for (int b = 0; b <= a; ++b) vt[a * (a + 1) / 2 + b] = (a == b) ? id[a] : Lc[a * 6 + b];
+#pragma unroll 1
+    for (int c = 0; c <= L; ++c) {
+        const double* rhs = bd + ((c < L) ? (S::B + c * 6) : S::GV);
+        double z[6];
+#pragma unroll
+        for (int i = 0; i < 6; ++i) {
+            double s = rhs[i];
+#pragma unroll
+            for (int k = 0; k < 6; ++k)
+                if (k < i) s = fma(-Lc[i * 6 + k], z[k], s);
+            z[i] = s * id[i];
+            vt[21 + c * 6 + i] = z[i];
+        }
+    }
+}
+
+// Back-substitution of one view by one thread: x = L^-T (z_g - Z^T dc)
+template <int MODEL>
+__device__ __forceinline__ void view_backsub_thread(const double* vt, const double* dc, double (&x)[6]) {
+    constexpr int L = ModelTraits<MODEL>::L;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        double s = vt[21 + L * 6 + i];
+#pragma unroll 1
+        for (int p = 0; p < L; ++p) s = fma(-vt[21 + p * 6 + i], dc[p], s);
+        x[i] = s;
+    }
+#pragma unroll
+    for (int i = 5; i >= 0; --i) {
+        double s = x[i];
+#pragma unroll
+        for (int k = 0; k < 6; ++k)
+            if (k > i) s = fma(-vt[k * (k + 1) / 2 + i], x[k], s);
+        x[i] = s * vt[i * (i + 1) / 2 + i];
+    }
+}
+
+template <int MODEL>
+__global__ void __launch_bounds__(kBatchThreads, 2) k_batch_lm(BatchDev d) {
+    using T = ModelTraits<MODEL>;
+    constexpr int L = T::L, NT = L * (L + 1) / 2, NWE = NT + L;
+    extern __shared__ __align__(16) double smem[];
+    const BatchSmem lay = batch_smem_layout(L, d.max_views, d.max_points, d.stage_points);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int prob = blockIdx.x;
+    const long long v0 = d.prob_view[prob];
+    const int M = (int)(d.prob_view[prob + 1] - v0);
+    const int K = L + 6 * M;
+    const int Kp = (L + 6 * d.max_views + 1) & ~1;
+    const long long pt0 = d.view_off[v0];
+    const int npts = (int)(d.view_off[v0 + M] - pt0);
+    double* gP = d.P + (long long)L * prob + 6 * v0;
+
+    double* sP = smem + lay.P;                                   // [2][Kp]
+    ViewC* sViews = reinterpret_cast<ViewC*>(smem + lay.views);  // [2][max_views]
+    double* sBD = smem + lay.bd;                                 // [M][97]
+    double* sVt = smem + lay.vt;                                 // [M][89]
+    double* sRedA = smem + lay.redA;                             // [kBatchWarps][64]
+    double* sA = sRedA + kBatchWarps * kNA;                      // [64]
+    double* sW = sA + kNA;                                       // [96]
+    double* sE = smem + lay.misc;                                // [kBatchWarps]
+    double* sdc = sE + 8;                                        // [L]
+    double* sScal = sdc + 16;                                    // lam, E_cur, E_trial, sse
+    int* sInt = reinterpret_cast<int*>(sScal + 8);               // cur, need_eval, done, iter
+
+    // ---- set-up: parameters, view constants, detections
+    for (int i = tid; i < K; i += kBatchThreads) sP[i] = gP[i];
+    const double *pX, *pY, *pZ, *pU, *pV;
+    if (d.stage_points) {
+        double* sp = smem + lay.pts;
+        const int n = d.max_points;
+        for (int i = tid; i < npts; i += kBatchThreads) {
+            sp[i] = d.X[pt0 + i]; sp[n + i] = d.Y[pt0 + i]; sp[2 * n + i] = d.Z[pt0 + i];
+            sp[3 * n + i] = d.U[pt0 + i]; sp[4 * n + i] = d.V[pt0 + i];
+        }
+        pX = sp; pY = sp + n; pZ = sp + 2 * n; pU = sp + 3 * n; pV = sp + 4 * n;
+    } else {
+        pX = d.X + pt0; pY = d.Y + pt0; pZ = d.Z + pt0; pU = d.U + pt0; pV = d.V + pt0;
+    }
+    if (tid == 0) {
+        sScal[0] = d.lam0; sScal[1] = 0.0; sScal[2] = 0.0; sScal[3] = 0.0;
+        sInt[0] = 0; sInt[1] = 1; sInt[2] = 0; sInt[3] = 0;
+    }
+    __syncthreads();
+    for (int v = tid; v < M; v += kBatchThreads) make_view(sP + L + 6 * v, sViews[v]);
+    __syncthreads();
+
+    // ---- the loop: src/calibrate.py:143-168
+    for (;;) {
+        const int cur = sInt[0];
+        const double lam = sScal[0];
+        const double* Pc = sP + cur * Kp;
+        double* Pt = sP + (cur ^ 1) * Kp;
+        const ViewC* vc = sViews + cur * d.max_views;
+        ViewC* vt_views = sViews + (cur ^ 1) * d.max_views;
+        if (sInt[1]) {
+            // sweep 1: B_v, D_v, g_v, one warp per view
+            for (int v = warp; v < M; v += kBatchWarps) {
+                const int s0 = (int)(d.view_off[v0 + v] - pt0), cnt = (int)(d.view_off[v0 + v + 1] - pt0) - s0;
+                double acc[kNBD];
+#pragma unroll
+                for (int i = 0; i < kNBD; ++i) acc[i] = 0.0;
+                for (int i = lane; i < cnt; i += 32) {
+                    PointOut<MODEL> o;
+                    point_eval<MODEL, true, true>(Pc, vc[v], pX[s0 + i], pY[s0 + i], pZ[s0 + i], pU[s0 + i], pV[s0 + i], o);
+                    accum_BD<MODEL>(o, acc);
+                }
+                warp_reduce_scatter<kNBD>(acc, lane);
+                double* row = sBD + v * kBDStride + lane * (kNBD / 32);
+#pragma unroll
+                for (int j = 0; j < kNBD / 32; ++j) row[j] = acc[j];
+            }
+            // sweep 2: A, g_c, E over the warp's views
+            {
+                double acc[kNA];
+#pragma unroll
+                for (int i = 0; i < kNA; ++i) acc[i] = 0.0;
+                double e = 0.0;
+                for (int v = warp; v < M; v += kBatchWarps) {
+                    const int s0 = (int)(d.view_off[v0 + v] - pt0), cnt = (int)(d.view_off[v0 + v + 1] - pt0) - s0;
+                    for (int i = lane; i < cnt; i += 32) {
+                        PointOut<MODEL> o;
+                        point_eval<MODEL, true, false>(Pc, vc[v], pX[s0 + i], pY[s0 + i], pZ[s0 + i], pU[s0 + i], pV[s0 + i], o);
+                        accum_A<MODEL>(o, acc, e);
+                    }
+                }
+                warp_reduce_scatter<kNA>(acc, lane);
+                e = warp_sum(e);
+                sRedA[warp * kNA + 2 * lane] = acc[0];
+                sRedA[warp * kNA + 2 * lane + 1] = acc[1];
+                if (lane == 0) sE[warp] = e;
+            }
+            __syncthreads();
+            if (tid < kNA) {
+                double s = sRedA[tid];
+#pragma unroll
+                for (int k = 1; k < kBatchWarps; ++k) s += sRedA[k * kNA + tid];
+                sA[tid] = s;
+            } else if (tid == kNA) {
+                double s = sE[0];
+#pragma unroll
+                for (int k = 1; k < kBatchWarps; ++k) s = __dadd_rn(s, sE[k]);
+                sScal[1] = s;
+            }
+        }
+        // Schur stage: one thread per view
+        for (int v = tid; v < M; v += kBatchThreads) view_schur_thread<MODEL>(sBD + v * kBDStride, lam, sVt + v * kVtStride);
+        __syncthreads();
+        // W = sum_v Z_v^T Z_v and w = sum_v Z_v^T z_g: one thread per entry
+        if (tid < NWE) {
+            int e = tid, p, c;
+            if (e < NT) { p = 0; while (e >= L - p) { e -= L - p; ++p; } c = p + e; }
+            else { p = e - NT; c = L; }
+            double s = 0.0;
+            for (int v = 0; v < M; ++v) {
+                const double* zp = sVt + v * kVtStride + 21 + p * 6;
+                const double* zc = sVt + v * kVtStride + 21 + c * 6;
+                double t = 0.0;
+#pragma unroll
+                for (int i = 0; i < 6; ++i) t = fma(zp[i], zc[i], t);
+                s += t;
+            }
+            sW[tid] = s;
+        }
+        __syncthreads();
+        // reduced solve by warp 0 -> dc, trial shared parameters
+        if (warp == 0) {
+            const double dc = solve_reduced_core<MODEL>(sA, sW, lam, lane, LdPlain());
+            if (lane < L) { sdc[lane] = dc; Pt[lane] = Pc[lane] + dc; }
+        }
+        __syncthreads();
+        // back-substitution, trial extrinsics and view constants: one thread per view
+        for (int v = tid; v < M; v += kBatchThreads) {
+            double x[6];
+            view_backsub_thread<MODEL>(sVt + v * kVtStride, sdc, x);
+#pragma unroll
+            for (int i = 0; i < 6; ++i) Pt[L + 6 * v + i] = Pc[L + 6 * v + i] + x[i];
+            make_view(Pt + L + 6 * v, vt_views[v]);
+        }
+        __syncthreads();
+        // trial cost
+        {
+            double e = 0.0;
+            for (int v = warp; v < M; v += kBatchWarps) {
+                const int s0 = (int)(d.view_off[v0 + v] - pt0), cnt = (int)(d.view_off[v0 + v + 1] - pt0) - s0;
+                for (int i = lane; i < cnt; i += 32) {
+                    PointOut<MODEL> o;
+                    point_eval<MODEL, false, false>(Pt, vt_views[v], pX[s0 + i], pY[s0 + i], pZ[s0 + i], pU[s0 + i], pV[s0 + i], o);
+                    e = __dadd_rn(e, fma(o.rv, o.rv, __dmul_rn(o.ru, o.ru)));
+                }
+            }
+            e = warp_sum(e);
+            if (lane == 0) sE[warp] = e;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            double E1 = sE[0];
+#pragma unroll
+            for (int k = 1; k < kBatchWarps; ++k) E1 = __dadd_rn(E1, sE[k]);
+            // accept / reject, lambda update, termination: src/calibrate.py:155-168
+            const double E = sScal[1];
+            const int it = sInt[3];
+            const bool acc = E1 < E;   // strict; NaN rejects
+            if (d.want_trace) {
+                double* tr = d.trace + ((long long)prob * d.max_iters + it) * 4;
+                tr[0] = E; tr[1] = E1; tr[2] = lam; tr[3] = acc ? 1.0 : 0.0;
+            }
+            double nl;
+            if (acc) { sInt[0] = cur ^ 1; nl = lam / 10.0; sInt[1] = 1; }
+            else     { nl = lam * 10.0; sInt[1] = 0; }
+            sScal[0] = nl;
+            sScal[3] = E;
+            sInt[3] = it + 1;
+            if (!(d.lam_min < nl && nl < d.lam_max) || E < d.err_min || it + 1 >= d.max_iters) sInt[2] = 1;
+        }
+        __syncthreads();
+        if (sInt[2]) break;
+    }
+    const double* Pf = sP + sInt[0] * Kp;
+    for (int i = tid; i < K; i += kBatchThreads) gP[i] = Pf[i];
+    if (tid == 0) { d.sse[prob] = sScal[3]; d.iters[prob] = sInt[3]; }
+}
+
+}  // namespace calib

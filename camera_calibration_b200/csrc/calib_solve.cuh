@@ -36,24 +36,28 @@ __host__ __device__ inline int a_slot(int i, int j) {
 // Lane i keeps row i of S in registers; the factorisation is right-looking (after column j every
 // lane updates the rest of its row), so the serial chain per column is one reciprocal square root,
 // one multiply and two shuffles.
-template <int MODEL>
-__device__ __forceinline__ void solve_reduced(const Dev& d, int lane) {
+struct LdCg { __device__ __forceinline__ double operator()(const double* p) const { return __ldcg(p); } };
+struct LdPlain { __device__ __forceinline__ double operator()(const double* p) const { return *p; } };
+
+// redA: the intrinsic-sweep slots (A and g_c), redW: W = sum Z^T Z (upper triangle) then w.
+// Returns dc[lane] for lane < L.
+template <int MODEL, class Ld>
+__device__ __forceinline__ double solve_reduced_core(const double* redA, const double* redW, double lam,
+                                                     int lane, Ld ld) {
     using T = ModelTraits<MODEL>;
     constexpr int L = T::L, ND = T::ND;
     using SA = SlotsA<ND>;
-    LmState* st = d.st;
-    const double lam = st->lam;
     const int i = lane < L ? lane : L - 1;       // idle lanes mirror the last row (no divergence)
     double row[L];
 #pragma unroll
     for (int j = 0; j < L; ++j) {
         const int lo = i < j ? i : j, hi = i < j ? j : i;
         const int sl = a_slot<ND>(lo, hi);
-        double a = sl >= 0 ? __ldcg(d.red + kRedA + sl) : 0.0;
+        double a = sl >= 0 ? ld(redA + sl) : 0.0;
         if (i == j) a = fma(lam, a, a);
-        row[j] = a - __ldcg(d.red + kRedW + tri(L, lo, hi));
+        row[j] = a - ld(redW + tri(L, lo, hi));
     }
-    double rhs = __ldcg(d.red + kRedA + SA::G + i) - __ldcg(d.red + kRedW + L * (L + 1) / 2 + i);
+    double rhs = ld(redA + SA::G + i) - ld(redW + L * (L + 1) / 2 + i);
     double inv[L];
 #pragma unroll
     for (int j = 0; j < L; ++j) {
@@ -63,9 +67,11 @@ __device__ __forceinline__ void solve_reduced(const Dev& d, int lane) {
         const double lij = row[j] * id;          // column j of the factor (rows >= j meaningful)
         row[j] = lij;
 #pragma unroll
-        for (int k = j + 1; k < L; ++k) {
-            const double lkj = __shfl_sync(0xffffffffu, lij, k);
-            row[k] = fma(-lij, lkj, row[k]);     // S[i][k] -= L[i][j] L[k][j]
+        for (int k = 0; k < L; ++k) {
+            if (k > j) {
+                const double lkj = __shfl_sync(0xffffffffu, lij, k);
+                row[k] = fma(-lij, lkj, row[k]);     // S[i][k] -= L[i][j] L[k][j]
+            }
         }
     }
     // L y = s (column oriented): y_j = rhs_j / L_jj, then rhs_i -= L_ij y_j for i > j
@@ -88,10 +94,18 @@ __device__ __forceinline__ void solve_reduced(const Dev& d, int lane) {
         if (i == j) rhs = xj;
         else if (i < j) rhs = fma(-mine, xj, rhs);
     }
+    return rhs;
+}
+
+template <int MODEL>
+__device__ __forceinline__ void solve_reduced(const Dev& d, int lane) {
+    constexpr int L = ModelTraits<MODEL>::L;
+    LmState* st = d.st;
+    const double dc = solve_reduced_core<MODEL>(d.red + kRedA, d.red + kRedW, st->lam, lane, LdCg());
     const int cur = st->cur;
     if (lane < L) {
-        d.delta[lane] = rhs;
-        d.Pbuf[(long long)(cur ^ 1) * d.K + lane] = d.Pbuf[(long long)cur * d.K + lane] + rhs;
+        d.delta[lane] = dc;
+        d.Pbuf[(long long)(cur ^ 1) * d.K + lane] = d.Pbuf[(long long)cur * d.K + lane] + dc;
     }
     if (lane == 0) st->E_cur = __ldcg(d.red + kRedE);
 }

@@ -136,9 +136,14 @@ int calib_comm_init(calib_t* h, int nranks, int rank, const void* id128);
  * long-lived communicator serve one calib_create/calib_lm_run/calib_destroy per calibration. */
 int calib_comm_share(calib_t* h, const calib_t* owner);
 
-/* Batch of independent calibrations (one thread block per problem, whole LM loop in one
- * launch).  problem_view_offsets[n_problems+1] indexes view_offsets; P is the concatenation
- * of the problems' parameter vectors; sse/iters have n_problems entries. */
+/* Batch of independent calibrations (a Python `for` over refineCalibrationParameters calls in the
+ * reference; BASELINE config 4): one thread block per problem, the whole LM loop in one launch,
+ * problems up to about 100 views.  problem_view_offsets[n_problems+1] indexes view_offsets
+ * (total_views+1, point offsets over ALL problems); P is the concatenation of the problems'
+ * parameter vectors (problem p starts at L p + 6 problem_view_offsets[p]); sse / iters have
+ * n_problems entries; trace (nullable): n_problems x maxIters x 4, rows (E, E', lambda,
+ * accepted), zero after a problem's last iteration.  Split the problems over GPUs by creating
+ * one handle per device: there is no communication between problems. */
 int calib_batch_create(calib_batch_t** out, int model, int64_t n_problems,
                        const int64_t* problem_view_offsets, const int64_t* view_offsets,
                        const double* model_pts, const double* sensor_pts, int device_id);
@@ -146,7 +151,7 @@ void calib_batch_destroy(calib_batch_t* h);
 const char* calib_batch_last_error(const calib_batch_t* h);
 int calib_batch_lm_run(calib_batch_t* h, double* P_inout, int maxIters, double lam0,
                        double lam_min, double lam_max, double err_min, double* sse_out,
-                       int* iters_out, double* device_ms);
+                       int* iters_out, double* trace, double* device_ms);
 
 #ifdef __cplusplus
 }

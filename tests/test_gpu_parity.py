@@ -264,3 +264,76 @@ def test_loop_modes_identical(golden):
         s3, P3, i3, t3 = prob.lm_run(g["P0"], 7)
         assert i3 == 7 and np.array_equal(t3, t1[:7])
         prob.close()
+
+
+# ---- batch of independent calibrations (BASELINE config 4) -------------------------------------
+def _batch_inputs(n, views=20):
+    probs = synth.batch_config(n, views)
+    cal = cc.Calibrator("radtan")
+    P0 = [cal._composeParameterVector(*p["init"]).ravel() for p in probs]
+    return probs, P0
+
+
+def test_batch_vs_oracle_and_single():
+    """Every problem of a batch must follow the same iterates as the oracle and as the
+    single-problem path (same device math, different mapping onto the GPU)."""
+    probs, P0 = _batch_inputs(6)
+    bp = cc.BatchProblem(0, [p["dets"] for p in probs])
+    sse, P, iters, tr, ms = bp.lm_run(np.concatenate(P0), 100, want_trace=True)
+    for j, sl in enumerate(bp.param_slices()):
+        offs, mp, sp = cc.flatten_detections(probs[j]["dets"])
+        so, Po, io, to = oc.lm(0, P0[j], offs, mp, sp, 100)
+        t = tr[j, :iters[j]]
+        stop = _check_trace(t, to)
+        assert stop >= 5
+        assert abs(sse[j] - so) < 1e-9 * so
+        assert param_relerr(P[sl], Po) < 1e-6         # past the plateau: see test_mid_size_vs_oracle
+        assert sse[j] == t[-1, 0]
+        # same iterates at the last pre-plateau iteration, against the single-problem CUDA path
+        prob = cc.Problem(0, offs, mp, sp)
+        _, Ps, _, _ = prob.lm_run(P0[j], stop)
+        prob.close()
+        bp1 = cc.BatchProblem(0, [probs[j]["dets"]])
+        _, Pb, itb, _, _ = bp1.lm_run(P0[j], stop)
+        bp1.close()
+        assert itb[0] == stop
+        assert param_relerr(Pb, Ps) < TOL_P
+        _, Pso, _, _ = oc.lm(0, P0[j], offs, mp, sp, stop)
+        assert param_relerr(Pb, Pso) < TOL_P
+    bp.close()
+
+
+def test_batch_golden_cases(golden):
+    """The reference's own cases as one-problem batches: radtan and fisheye, noise-free counts exact."""
+    for case in ("cfg1", "cfg2", "itest"):
+        g = golden(case)
+        offs = g["view_offsets"]
+        dets = [(g["sensor_pts"][offs[i]:offs[i + 1]], g["model_pts"][offs[i]:offs[i + 1]]) for i in range(len(offs) - 1)]
+        bp = cc.BatchProblem(int(g["model"]), [dets])
+        sse, P, iters, tr, ms = bp.lm_run(g["P0"], int(g["maxIters"]), want_trace=True)
+        _check_trace(tr[0, :iters[0]], g["trace"])
+        assert param_relerr(P, g["Pfinal"]) < TOL_P
+        if case in ("cfg1", "itest"):
+            assert iters[0] == int(g["iters"]) and sse[0] < 1e-12
+        bp.close()
+
+
+def test_batch_ragged_and_errors():
+    probs, P0 = _batch_inputs(3)
+    # problems with different numbers of views in one batch
+    dets = [probs[0]["dets"][:7], probs[1]["dets"], probs[2]["dets"][:13]]
+    Pcat = np.concatenate([P0[0][:10 + 42], P0[1], P0[2][:10 + 78]])
+    bp = cc.BatchProblem(0, dets)
+    sse, P, iters, tr, ms = bp.lm_run(Pcat, 100, want_trace=True)
+    for j, sl in enumerate(bp.param_slices()):
+        offs, mp, sp = cc.flatten_detections(dets[j])
+        so, Po, io, to = oc.lm(0, Pcat[sl], offs, mp, sp, 100)
+        _check_trace(tr[j, :iters[j]], to)
+        assert abs(sse[j] - so) < 1e-9 * so
+    with pytest.raises(ValueError):
+        bp.lm_run(Pcat[:-1], 10)
+    with pytest.raises(cc.CalibError):
+        bp.lm_run(Pcat, 0)
+    bp.close()
+    with pytest.raises(cc.CalibError):
+        cc.BatchProblem(0, [probs[0]["dets"] * 8])      # 160 views: beyond the one-block path

@@ -192,6 +192,172 @@ def pinned_copy(L, arr):
     return view, ptr
 
 
+# ---- config 4: batch of independent calibrations, split over GPUs with no communication ----------
+COST_FLOPS_PER_POINT = 100     # residual-only sweep
+
+
+def load_batch(n_problems):
+    from camera_calibration_b200 import synth
+    import camera_calibration_b200 as cc
+    probs = synth.batch_config(n_problems, procs=min(os.cpu_count() or 1, 32))
+    cal = cc.Calibrator(0)
+    P0 = [cal._composeParameterVector(*p["init"]).ravel() for p in probs]
+    return probs, P0
+
+
+def batch_cpu_baseline(probs, P0, sample):
+    """oracle port on the host cores: one problem per thread (ctypes releases the GIL)."""
+    import oracle_c
+    import camera_calibration_b200 as cc
+    from concurrent.futures import ThreadPoolExecutor
+    threads = os.cpu_count() or 1
+    idx = list(range(min(sample, len(probs))))
+    flat = [cc.flatten_detections(probs[j]["dets"]) for j in idx]
+
+    def one(k):
+        offs, mp, sp = flat[k]
+        return oracle_c.lm(0, P0[idx[k]], offs, mp, sp, MAX_ITERS, nthreads=1)[2]
+    one(0)
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(threads) as ex:
+        its = list(ex.map(one, range(len(idx))))
+    dt = time.perf_counter() - t0
+    return sum(its) / dt, threads, len(idx), dt
+
+
+def run_batch(args):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    n_all = args.problems
+    probs, P0 = load_batch(n_all)
+    cfg = {"workload": f"cfg4: {n_all} independent 20-view calibrations, 9x6 board, radtan, sigma 0.1 px",
+           "model": "radtan", "problems": n_all, "views_per_problem": 20,
+           "points": int(sum(len(s) for p in probs for s, m in p["dets"])), "max_iters": MAX_ITERS,
+           "init": "perturbed ground truth, RandomState(problem index)",
+           "step": "all problems refined to termination in one launch",
+           "parallelism": f"problems split over {world} GPU(s), no communication",
+           "l2": "flushed (256 MB write) before every timed step"}
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        import oracle_c  # noqa: F401
+        val, threads, ns, dt = batch_cpu_baseline(probs, P0, args.cpu_sample)
+        line = {"impl": "reference", "metric": "lm_iterations_per_sec", "value": val, "unit": "LM iterations/s",
+                "n_gpus": args.gpus, "steps": 1, "warmup": 0, "ms_per_step": 1e3 * dt, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg,
+                "cpu_baseline": {"value": val, "unit": "LM iterations/s", "cores": threads, "kind": "port",
+                                 "sample": f"the first {ns} problems, one per host thread ({dt:.2f} s); C restatement "
+                                           "of the reference's path (oracle/calib_oracle.c)"},
+                "e2e": {"value": val, "unit": "LM iterations/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line), flush=True)
+        return
+    import torch
+    import camera_calibration_b200 as cc
+    from camera_calibration_b200 import _lib
+    torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    lo, hi = n_all * rank // world, n_all * (rank + 1) // world
+    mine, P0m = probs[lo:hi], np.concatenate(P0[lo:hi])
+    views = np.array([len(p["dets"]) for p in mine], dtype=np.int64)
+    pv = np.concatenate([[0], np.cumsum(views)]).astype(np.int64)
+    voffs, mp, sp = cc.flatten_detections([det for p in mine for det in p["dets"]])
+    lib = _lib.lib()
+    mp_pin, mp_ptr = pinned_copy(lib, mp)
+    sp_pin, sp_ptr = pinned_copy(lib, sp)
+    bp = cc.BatchProblem(0, None, device=local, csr=(pv, voffs, mp_pin, sp_pin))
+    flush = torch.empty(64 << 20, dtype=torch.float32, device="cuda")
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        bp.lm_run(P0m, MAX_ITERS)
+    barrier()
+    tot_ms = tot_it = 0
+    with ClockSampler(local) as clk:
+        for _ in range(args.steps):
+            flush.fill_(1.0)
+            torch.cuda.synchronize()
+            sse, P, iters, _, ms = bp.lm_run(P0m, MAX_ITERS)
+            tot_ms += ms
+            tot_it += int(iters.sum())
+        barrier()
+    if world > 1:
+        t = torch.tensor([tot_ms, float(tot_it)], dtype=torch.float64, device="cuda")
+        tm = t.clone()
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        tot_ms, tot_it = float(tm[0].item()), int(t[1].item())
+    value = tot_it / (tot_ms * 1e-3)
+
+    def e2e_step():
+        b2 = cc.BatchProblem(0, None, device=local, csr=(pv, voffs, mp_pin, sp_pin))
+        _, _, it, _, _ = b2.lm_run(P0m, MAX_ITERS)
+        b2.close()
+        return int(it.sum())
+    e2e_step()
+    barrier()
+    n_e2e = max(3, min(args.steps, 10))
+    t0 = time.perf_counter()
+    it_e2e = sum(e2e_step() for _ in range(n_e2e))
+    barrier()
+    dt = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([dt, float(it_e2e)], dtype=torch.float64, device="cuda")
+        tm = t.clone()
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        dt, it_e2e = float(tm[0].item()), int(t[1].item())
+    e2e = {"value": it_e2e / dt, "unit": "LM iterations/s",
+           "h2d_bytes_per_step": int(40 * voffs[-1] + 8 * len(P0m) + 8 * (len(voffs) + len(pv))),
+           "d2h_bytes_per_step": int(8 * len(P0m) + 12 * len(mine)), "ms_per_step": 1e3 * dt / n_e2e,
+           "api": "C-ABI per step and rank: calib_batch_create(page-locked CSR host buffers) + "
+                  "calib_batch_lm_run(host P) + calib_batch_destroy"}
+    # roofline: FP64 work actually required by the traces of one run / kernel time
+    sse, P, iters, tr, ms = bp.lm_run(P0m, MAX_ITERS, want_trace=True)
+    npts = np.array([sum(len(s) for s, m in p["dets"]) for p in mine], dtype=np.float64)
+    acc = tr[:, :, 3].sum(axis=1)
+    last_acc = np.array([tr[j, iters[j] - 1, 3] for j in range(len(mine))])
+    evals = 1 + acc - last_acc
+    flops = float((npts * (evals * FLOPS_PER_POINT[0] + iters * COST_FLOPS_PER_POINT)).sum())
+    roof = None
+    cpu = None
+    if rank == 0:
+        peak64 = cc.calibrate.fp64_peak_tflops(local)
+        sse2, _, iters2, _, ms2 = bp.lm_run(P0m, MAX_ITERS)
+        roof = {"bound": "fp64", "kernel": "k_batch_lm", "achieved": flops / (ms2 * 1e-3) / 1e12, "peak": peak64,
+                "unit": "TFLOP/s", "frac": flops / (ms2 * 1e-3) / 1e12 / peak64, "traffic": None,
+                "peak_source": "DFMA micro-benchmark in this run (calib_measure_fp64_peak)",
+                "flops": "sum over problems of points x (Jacobian passes x 1012 + iterations x 100)",
+                "launch_ms": ms2, "problems_per_launch": len(mine),
+                "mean_iterations": float(iters.mean()), "mean_jacobian_passes": float(evals.mean())}
+        if world == 1 and not args.no_cpu_baseline:
+            v, threads, ns, dtc = batch_cpu_baseline(probs, P0, args.cpu_sample)
+            cpu = {"value": v, "unit": "LM iterations/s", "cores": threads, "kind": "port",
+                   "sample": f"the first {ns} problems, one per host thread ({dtc:.2f} s); C restatement of the "
+                             "reference's path (oracle/calib_oracle.c)"}
+        line = {"metric": "lm_iterations_per_sec", "value": value, "unit": "LM iterations/s", "n_gpus": world,
+                "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": tot_ms / args.steps,
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+                "data": "synthetic", "config": cfg, "calibrations_per_sec": n_all * args.steps / (tot_ms * 1e-3),
+                "e2e": e2e, "gpu_launches": int(args.steps), "roofline": roof, "cpu_baseline": cpu,
+                "clocks": clk.summary()}
+        print(json.dumps(line), flush=True)
+    bp.close()
+    lib.calib_host_free(mp_ptr)
+    lib.calib_host_free(sp_ptr)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -203,7 +369,13 @@ def main():
     ap.add_argument("--segment", type=int, default=0)
     ap.add_argument("--loop-mode", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--problems", type=int, default=8192)
+    ap.add_argument("--cpu-sample", type=int, default=512)
     args = ap.parse_args()
+    if args.workload == "cfg4":
+        if args.steps == 100:
+            args.steps = 10
+        return run_batch(args)
     if args.impl == "reference":
         return run_reference_arm(args)
     args.warmup = max(args.warmup, 3)

@@ -247,15 +247,23 @@ class BatchProblem:
     """A batch of independent calibrations resident on one GPU (calib_batch_t): one thread block
     per problem, the whole LM loop in one launch.  problems: list of allDetections lists."""
 
-    def __init__(self, model, problems, device=0):
+    def __init__(self, model, problems, device=0, csr=None):
+        """problems: list of allDetections lists; or csr = (problem_view_offsets, view_offsets,
+        model_pts, sensor_pts) already flattened (e.g. in page-locked memory)."""
         self.model = distortion.model_id_of(model)
         self.L = 10 if self.model == distortion.RADTAN else 9
-        self.n = len(problems)
-        views = [len(p) for p in problems]
-        self.prob_view = np.zeros(self.n + 1, dtype=np.int64)
-        np.cumsum(views, out=self.prob_view[1:])
-        flat = [det for p in problems for det in p]
-        self.view_offsets, mp, sp = flatten_detections(flat)
+        if csr is None:
+            views = [len(p) for p in problems]
+            self.n = len(problems)
+            self.prob_view = np.zeros(self.n + 1, dtype=np.int64)
+            np.cumsum(views, out=self.prob_view[1:])
+            flat = [det for p in problems for det in p]
+            self.view_offsets, mp, sp = flatten_detections(flat)
+        else:
+            self.prob_view = np.ascontiguousarray(csr[0], dtype=np.int64)
+            self.view_offsets = np.ascontiguousarray(csr[1], dtype=np.int64)
+            self.n = len(self.prob_view) - 1
+            mp, sp = as_f64(csr[2]).reshape(-1, 3), as_f64(csr[3]).reshape(-1, 2)
         self.total_params = self.L * self.n + 6 * int(self.prob_view[-1])
         self._L = _lib.lib()
         self._h = ctypes.c_void_p()

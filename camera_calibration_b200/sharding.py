@@ -1,0 +1,49 @@
+"""Host-side sharding of one large calibration over ranks: contiguous view
+ranges balanced by point count; every rank keeps the L shared parameters and the extrinsics of
+its own views.  The reduced system is a sum over views, so a rank's share is the same computation
+on fewer views followed by an all-reduce (the C-ABI does it with NCCL on the device;
+`allreduce_reduced_system` is the host-side statement of the same step for gloo tests)."""
+import numpy as np
+
+
+def view_bounds(counts, world):
+    """[b_0=0, b_1, ..., b_world=M]: rank r owns views b_r .. b_{r+1}-1."""
+    counts = np.asarray(counts, dtype=np.int64)
+    cum = np.concatenate([[0], np.cumsum(counts)])
+    total = cum[-1]
+    b = [int(np.searchsorted(cum, total * r / world, side="left")) for r in range(world)] + [len(counts)]
+    b[0] = 0
+    for r in range(1, world + 1):        # monotone even for degenerate inputs
+        b[r] = max(b[r], b[r - 1])
+    return b
+
+
+def view_range(allDetections, world, rank):
+    b = view_bounds([len(s) for s, m in allDetections], world)
+    return b[rank], b[rank + 1]
+
+
+def local_params(P, L, lo, hi):
+    P = np.asarray(P, dtype=np.float64).ravel()
+    return np.concatenate([P[:L], P[L + 6 * lo:L + 6 * hi]])
+
+
+def merge_params(parts, L, M):
+    """parts: iterable of (lo, hi, Plocal) -> the full parameter vector (shared values from the first)."""
+    parts = list(parts)
+    P = np.empty(L + 6 * M)
+    P[:L] = parts[0][2][:L]
+    for lo, hi, p in parts:
+        P[L + 6 * lo:L + 6 * hi] = np.asarray(p)[L:]
+    return P
+
+
+def allreduce_reduced_system(local_S, local_s, local_E, dist, group=None):
+    """Sum of the ranks' Schur complements, right-hand sides and costs (what ncclAllReduce does
+    on the device to the 161-double `red` block)."""
+    import torch
+    flat = torch.from_numpy(np.concatenate([np.asarray(local_S).ravel(), np.asarray(local_s).ravel(), [local_E]]))
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    out = flat.numpy()
+    n = np.asarray(local_s).size
+    return out[:n * n].reshape(n, n), out[n * n:n * n + n], float(out[-1])

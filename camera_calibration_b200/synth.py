@@ -108,14 +108,22 @@ def config(name, scale=1.0):
     raise ValueError("unknown config " + name)
 
 
-def batch_config(n_problems, views=20):
-    """cfg4: independent 20-view calibrations of the 9x6 board; problem j uses view seeds
-    20*j .. 20*j+19 and RandomState(j) for its perturbed initial guess."""
+def _batch_one(args):
+    j, views = args
     c = checkerboard_corners(9, 6, 0.050)
-    out = []
-    for j in range(n_problems):
-        dets, poses = make_dataset(c, A_SYNTHETIC, K_RADTAN, "radtan", 1440, 1080, views, 0.1,
-                                   view_seed_base=views * j)
-        init = perturbed_initial(A_SYNTHETIC, K_RADTAN, poses, np.random.RandomState(j))
-        out.append(dict(model=0, dets=dets, poses=poses, init=init))
-    return out
+    dets, poses = make_dataset(c, A_SYNTHETIC, K_RADTAN, "radtan", 1440, 1080, views, 0.1,
+                               view_seed_base=views * j)
+    init = perturbed_initial(A_SYNTHETIC, K_RADTAN, poses, np.random.RandomState(j))
+    return dict(model=0, dets=dets, poses=poses, init=init)
+
+
+def batch_config(n_problems, views=20, procs=1):
+    """cfg4: independent 20-view calibrations of the 9x6 board; problem j uses view seeds
+    20*j .. 20*j+19 and RandomState(j) for its perturbed initial guess.  procs > 1 generates the
+    problems in worker processes (the per-view seeding makes the result independent of it)."""
+    jobs = [(j, views) for j in range(n_problems)]
+    if procs <= 1 or n_problems < 64:
+        return [_batch_one(a) for a in jobs]
+    import multiprocessing as mp
+    with mp.get_context("fork").Pool(procs) as pool:
+        return pool.map(_batch_one, jobs, chunksize=max(1, n_problems // (8 * procs)))

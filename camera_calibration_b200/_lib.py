@@ -8,7 +8,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
-SO_PATH = os.path.join(_HERE, "libcalib_b200.so")
+SO_PATH = os.environ.get("CALIB_B200_SO") or os.path.join(_HERE, "libcalib_b200.so")   # override: kernel-variant experiments
 HEADER = os.path.join(_HERE, "..", "include", "calib_b200.h")
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O3", "-lineinfo",
@@ -86,6 +86,7 @@ def lib():
         "calib_num_points": (c_i64, [_vp]),
         "calib_set_segment": (c_int, [_vp, c_int]),
         "calib_set_loop_mode": (c_int, [_vp, c_int]),
+        "calib_set_cost_staging": (c_int, [_vp, c_int]),
         "calib_host_alloc": (_vp, [ctypes.c_size_t]),
         "calib_host_free": (None, [_vp]),
         "calib_project": (c_int, [_vp, _d, _d]),
@@ -103,6 +104,7 @@ def lib():
         "calib_last_run_stats": (c_int, [_vp, _d, _i64, _i64]),
         "calib_set_profiling": (c_int, [_vp, c_int]),
         "calib_kernel_time": (c_int, [_vp, c_int, _d, _i64]),
+        "calib_time_kernel": (c_int, [_vp, _d, c_dbl, c_int, c_int, c_int, _d]),
         "calib_measure_fp64_peak": (c_int, [c_int, _d]),
         "calib_flush_l2": (c_int, [_vp]),
         "calib_comm_unique_id": (c_int, [_vp]),

@@ -232,6 +232,17 @@ class Problem:
                                               ctypes.byref(n)))
         return ms.value, n.value
 
+    def set_cost_staging(self, mode):
+        """-1 auto, 0 plain loads, 1 bulk-copy (TMA) ring for the trial-cost sweep"""
+        self._check(self._L.calib_set_cost_staging(self._h, int(mode)))
+
+    def time_kernel(self, P, which, reps=20, lam=1e-3, flush=False):
+        """average device microseconds of one kernel (0 eval, 1 schur, 2 backsub, 3 cost)"""
+        us = ctypes.c_double()
+        self._check(self._L.calib_time_kernel(self._h, dptr(self._P(P)), float(lam), int(which), int(reps),
+                                              1 if flush else 0, ctypes.cast(ctypes.byref(us), _lib._d)))
+        return us.value
+
     def flush_l2(self):
         self._check(self._L.calib_flush_l2(self._h))
 

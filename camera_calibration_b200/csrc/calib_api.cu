@@ -44,6 +44,7 @@ struct calib_handle {
     cudaGraphExec_t graph = nullptr;       // one iteration (host-driven loop)
     cudaGraphExec_t loop_graph = nullptr;  // WHILE node around the iteration (device-driven loop)
     int loop_mode = 0;                     // 0 auto, 1 host-driven, 2 device WHILE graph
+    int cost_tma = -1;                     // -1 auto (by size), 0 plain loads, 1 bulk-copy ring
     LmState* h_state = nullptr;   // pinned
     double* h_pinned = nullptr;   // pinned scratch (kRedN + 8 doubles)
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -203,13 +204,21 @@ static void drop_graph(calib_handle* h) {
 // Cuts the N points into n_warps contiguous, near-equal chunks (one per persistent warp) and each
 // chunk into pieces at the view boundaries.
 static void cut_points(const std::vector<int64_t>& offs, int64_t M, int64_t N, int n_warps,
-                       std::vector<Piece>& pieces, std::vector<int>& chunk) {
+                       std::vector<Piece>& pieces, std::vector<int>& chunk, std::vector<int>& chunk_end) {
     pieces.clear();
     chunk.assign((size_t)n_warps + 1, 0);
+    chunk_end.assign((size_t)n_warps, 0);
+    // boundaries on multiples of 32 points: the windows the bulk copies fetch are 256-byte aligned
+    auto bound = [&](int k) -> int64_t {
+        if (k >= n_warps) return N;
+        const int64_t b = (int64_t)((__int128)N * k / n_warps);
+        return std::min<int64_t>(N, (b + 16) / 32 * 32);
+    };
     int64_t v = 0;
     for (int k = 0; k < n_warps; ++k) {
-        int64_t s = (int64_t)((__int128)N * k / n_warps), e = (int64_t)((__int128)N * (k + 1) / n_warps);
+        int64_t s = bound(k), e = bound(k + 1);
         chunk[k] = (int)pieces.size();
+        chunk_end[k] = (int)e;
         while (s < e) {
             while (v < M && offs[v + 1] <= s) ++v;
             const int64_t cnt = std::min(e, offs[v + 1]) - s;
@@ -236,9 +245,9 @@ static int build_tasks(calib_handle* h, int seg) {
         co_warps = (int)std::min<int64_t>((int64_t)h->n_sm * kBlockWarps * 2, by_size);
     }
     std::vector<Piece> evp, cop;
-    std::vector<int> evc, coc, vp((size_t)M + 1, 0);
-    cut_points(h->view_offsets, M, N, ev_warps, evp, evc);
-    cut_points(h->view_offsets, M, N, co_warps, cop, coc);
+    std::vector<int> evc, coc, eve, coe, vp((size_t)M + 1, 0);
+    cut_points(h->view_offsets, M, N, ev_warps, evp, evc, eve);
+    cut_points(h->view_offsets, M, N, co_warps, cop, coc, coe);
     {   // piece range of every view (pieces are in view order)
         size_t p = 0;
         for (int64_t v = 0; v < M; ++v) {
@@ -252,9 +261,18 @@ static int build_tasks(calib_handle* h, int seg) {
     d.co_warps = co_warps; d.co_blocks = (co_warps + kBlockWarps - 1) / kBlockWarps;
     d.sc_blocks = (int)std::max<int64_t>(1, std::min<int64_t>((M + kBlockWarps - 1) / kBlockWarps, 2 * h->n_sm));
     Arena a;
-    const size_t o_evp = a.reserve<Piece>(evp.size()), o_evc = a.reserve<int>(evc.size());
+    auto records = [](const std::vector<Piece>& pc, const std::vector<int>& ch, const std::vector<int>& ce) {
+        std::vector<WarpRec> r(ch.size() - 1);
+        for (size_t k = 0; k + 1 < ch.size(); ++k) {
+            r[k].p0 = ch[k]; r[k].p1 = ch[k + 1]; r[k].end = ce[k]; r[k].pad1 = 0;
+            r[k].first = ch[k] < ch[k + 1] ? pc[ch[k]] : Piece{0, 0, 0, 0};
+        }
+        return r;
+    };
+    const std::vector<WarpRec> evr = records(evp, evc, eve), cor = records(cop, coc, coe);
+    const size_t o_evp = a.reserve<Piece>(evp.size()), o_evc = a.reserve<WarpRec>(evr.size());
     const size_t o_vp = a.reserve<int>(vp.size());
-    const size_t o_cop = a.reserve<Piece>(cop.size()), o_coc = a.reserve<int>(coc.size());
+    const size_t o_cop = a.reserve<Piece>(cop.size()), o_coc = a.reserve<WarpRec>(cor.size());
     const size_t meta_bytes = a.bytes;
     const size_t o_pA = a.reserve<double>((size_t)d.ev_blocks * kNA), o_pE = a.reserve<double>(d.ev_blocks);
     const size_t o_pBD = a.reserve<double>((size_t)std::max(d.ev_pieces, 1) * kNBD);
@@ -264,14 +282,14 @@ static int build_tasks(calib_handle* h, int seg) {
     // one upload for the five index tables
     std::vector<char> meta(meta_bytes, 0);
     memcpy(meta.data() + o_evp, evp.data(), evp.size() * sizeof(Piece));
-    memcpy(meta.data() + o_evc, evc.data(), evc.size() * sizeof(int));
+    memcpy(meta.data() + o_evc, evr.data(), evr.size() * sizeof(WarpRec));
     memcpy(meta.data() + o_vp, vp.data(), vp.size() * sizeof(int));
     memcpy(meta.data() + o_cop, cop.data(), cop.size() * sizeof(Piece));
-    memcpy(meta.data() + o_coc, coc.data(), coc.size() * sizeof(int));
+    memcpy(meta.data() + o_coc, cor.data(), cor.size() * sizeof(WarpRec));
     CUDA_TRY(h, cudaMemcpyAsync(a.base, meta.data(), meta_bytes, cudaMemcpyHostToDevice, h->stream));
     CUDA_TRY(h, cudaStreamSynchronize(h->stream));   // meta is a local
-    d.ev_piece = a.at<Piece>(o_evp); d.ev_chunk = a.at<int>(o_evc); d.view_piece = a.at<int>(o_vp);
-    d.co_piece = a.at<Piece>(o_cop); d.co_chunk = a.at<int>(o_coc);
+    d.ev_piece = a.at<Piece>(o_evp); d.ev_rec = a.at<WarpRec>(o_evc); d.view_piece = a.at<int>(o_vp);
+    d.co_piece = a.at<Piece>(o_cop); d.co_rec = a.at<WarpRec>(o_coc);
     d.partA = a.at<double>(o_pA); d.partE = a.at<double>(o_pE); d.partBD = a.at<double>(o_pBD);
     d.partW = a.at<double>(o_pW); d.partC = a.at<double>(o_pC);
     return CALIB_OK;
@@ -320,12 +338,22 @@ extern "C" int calib_create(calib_t** out, int model, int64_t M, const int64_t* 
 #define TRY_(call) do { int rc__ = [&]() -> int { CUDA_TRY(h, call); return 0; }(); if (rc__) { g_last_error = h->err; return bail(rc__); } } while (0)
     TRY_(cudaSetDevice(device_id));
     pool_keep_memory(device_id);
+    {   // the per-warp rings of the cost pass exceed the 48 KB default
+        static bool once = false;
+        if (!once) {
+            cudaFuncSetAttribute(k_cost<0, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCostDynSmem);
+            cudaFuncSetAttribute(k_cost<0, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCostDynSmem);
+            cudaFuncSetAttribute(k_cost<1, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCostDynSmem);
+            cudaFuncSetAttribute(k_cost<1, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCostDynSmem);
+            once = true;
+        }
+    }
     TRY_(cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, device_id));
     { int rc = ctx_acquire(h); if (rc) { g_last_error = h->err; return bail(rc); } }
     Dev& d = h->dev;
     d.model = model; d.L = h->L; d.M = (int)M; d.N = N; d.K = h->K;
     {
-        const size_t n = (size_t)std::max<int64_t>(N, 1);
+        const size_t n = ((size_t)std::max<int64_t>(N, 1) + 31) / 32 * 32;   // array stride: 256-byte aligned
         Arena a;
         const size_t o_soa = a.reserve<double>(5 * n + 64);
         const size_t o_P = a.reserve<double>((size_t)2 * h->K), o_views = a.reserve<ViewC>((size_t)2 * M);
@@ -397,6 +425,14 @@ extern "C" int calib_set_loop_mode(calib_t* h, int mode) {
     return CALIB_OK;
 }
 
+extern "C" int calib_set_cost_staging(calib_t* h, int mode) {
+    if (!h) return fail(nullptr, CALIB_E_ARG, "NULL handle");
+    if (mode < -1 || mode > 1) return fail(h, CALIB_E_ARG, "calib_set_cost_staging: -1 auto, 0 loads, 1 bulk copies");
+    h->cost_tma = mode;
+    drop_graph(h);
+    return CALIB_OK;
+}
+
 extern "C" void* calib_host_alloc(size_t bytes) {
     void* p = nullptr;
     if (cudaMallocHost(&p, std::max<size_t>(bytes, 1)) != cudaSuccess) {
@@ -443,7 +479,7 @@ void enqueue_schur(calib_handle* h, Launcher& ln, int fuse_solve) {
     const Dev& d = h->dev;
     cudaEvent_t a, b;
     ln.begin(&a, &b);
-    k_schur<MODEL><<<d.sc_blocks + 1, kBlockThreads, 0, h->stream>>>(d, fuse_solve);
+    k_schur<MODEL><<<d.sc_blocks, kBlockThreads, 0, h->stream>>>(d, fuse_solve);
     ln.end(KSCHUR, a, b);
     ln.count += 1;
 }
@@ -472,8 +508,15 @@ void enqueue_cost(calib_handle* h, Launcher& ln, int fuse_accept) {
     const Dev& d = h->dev;
     cudaEvent_t a, b;
     ln.begin(&a, &b);
-    if (d.use_cond) k_cost<MODEL, true><<<d.co_blocks, kBlockThreads, 0, h->stream>>>(d, fuse_accept);
-    else k_cost<MODEL, false><<<d.co_blocks, kBlockThreads, 0, h->stream>>>(d, fuse_accept);
+    // bulk-copy ring when the detections cannot stay in L2 between the sweeps, plain loads otherwise
+    const bool tma = h->cost_tma >= 0 ? h->cost_tma != 0 : (size_t)h->N * 40 > ((size_t)96 << 20);
+    if (tma) {
+        if (d.use_cond) k_cost<MODEL, true, true><<<d.co_blocks, kBlockThreads, kCostDynSmem, h->stream>>>(d, fuse_accept);
+        else k_cost<MODEL, false, true><<<d.co_blocks, kBlockThreads, kCostDynSmem, h->stream>>>(d, fuse_accept);
+    } else {
+        if (d.use_cond) k_cost<MODEL, true, false><<<d.co_blocks, kBlockThreads, 0, h->stream>>>(d, fuse_accept);
+        else k_cost<MODEL, false, false><<<d.co_blocks, kBlockThreads, 0, h->stream>>>(d, fuse_accept);
+    }
     ln.end(KCOST, a, b);
     ln.count += 1;
 }
@@ -841,6 +884,54 @@ extern "C" int calib_lm_step(calib_t* h, const double* P, double lam, double* de
     if (!delta) return fail(h, CALIB_E_ARG, "calib_lm_step: delta is NULL");
     RC(eval_system(h, P, lam, true));
     CUDA_TRY(h, cudaMemcpy(delta, h->dev.delta, (size_t)h->K * sizeof(double), cudaMemcpyDeviceToHost));
+    return CALIB_OK;
+}
+
+// Average device time of ONE kernel of the iteration, launched `reps` times back to back at P with
+// damping lam (events around the whole batch, so launch gaps between identical independent
+// launches are included but no host time).  flush != 0: the 256 MB L2 flush before every launch
+// (then the time of the flush kernel alone is measured the same way and subtracted).
+extern "C" int calib_time_kernel(calib_t* h, const double* P, double lam, int which, int reps, int flush,
+                                 double* avg_us) {
+    RC(check_handle(h));
+    if (!P || !avg_us || reps <= 0 || which < 0 || which > 3) return fail(h, CALIB_E_ARG, "calib_time_kernel: bad args");
+    h->cur = 0;
+    h->dev.use_cond = 0;
+    RC(upload_to(h, P, 0));
+    RC(push_state(h, lam, 0, 0, 0, 1 << 30));
+    RC(make_views(h, 1));
+    Launcher ln{h, false};
+    auto one = [&](int k) {
+        if (h->model == 0) {
+            if (k == 0) enqueue_eval<0>(h, ln); else if (k == 1) enqueue_schur<0>(h, ln, 1);
+            else if (k == 2) enqueue_backsub<0>(h, ln); else enqueue_cost<0>(h, ln, 0);
+        } else {
+            if (k == 0) enqueue_eval<1>(h, ln); else if (k == 1) enqueue_schur<1>(h, ln, 1);
+            else if (k == 2) enqueue_backsub<1>(h, ln); else enqueue_cost<1>(h, ln, 0);
+        }
+    };
+    for (int k = 0; k < 4; ++k) one(k);       // a full iteration first: every input of `which` is valid
+    RC(sync(h));
+    if (flush && !h->l2buf) RC(calib_flush_l2(h));
+    const long long nfl = (long long)(h->l2bytes / sizeof(double));
+    float ms_flush = 0.f, ms = 0.f;
+    if (flush) {
+        CUDA_TRY(h, cudaEventRecord(h->ev0, h->stream));
+        for (int r = 0; r < reps; ++r) k_fill<<<1184, 256, 0, h->stream>>>(h->l2buf, nfl, 1.0);
+        CUDA_TRY(h, cudaEventRecord(h->ev1, h->stream));
+        RC(sync(h));
+        CUDA_TRY(h, cudaEventElapsedTime(&ms_flush, h->ev0, h->ev1));
+    }
+    for (int r = 0; r < 3; ++r) one(which);
+    CUDA_TRY(h, cudaEventRecord(h->ev0, h->stream));
+    for (int r = 0; r < reps; ++r) {
+        if (flush) k_fill<<<1184, 256, 0, h->stream>>>(h->l2buf, nfl, 1.0);
+        one(which);
+    }
+    CUDA_TRY(h, cudaEventRecord(h->ev1, h->stream));
+    RC(sync(h));
+    CUDA_TRY(h, cudaEventElapsedTime(&ms, h->ev0, h->ev1));
+    *avg_us = 1e3 * (double)(ms - ms_flush) / reps;
     return CALIB_OK;
 }
 

@@ -211,7 +211,7 @@ __global__ void __launch_bounds__(kBatchThreads, 2) k_batch_lm(BatchDev d) {
                 double s = sE[0];
 #pragma unroll
                 for (int k = 1; k < kBatchWarps; ++k) s = __dadd_rn(s, sE[k]);
-                sScal[1] = s;
+                if (sInt[3] == 0) sScal[1] = s;      // later: the trial cost of the last accepted step
             }
         }
         // Schur stage: one thread per view
@@ -277,7 +277,7 @@ __global__ void __launch_bounds__(kBatchThreads, 2) k_batch_lm(BatchDev d) {
                 tr[0] = E; tr[1] = E1; tr[2] = lam; tr[3] = acc ? 1.0 : 0.0;
             }
             double nl;
-            if (acc) { sInt[0] = cur ^ 1; nl = lam / 10.0; sInt[1] = 1; }
+            if (acc) { sInt[0] = cur ^ 1; nl = lam / 10.0; sInt[1] = 1; sScal[1] = E1; }
             else     { nl = lam * 10.0; sInt[1] = 0; }
             sScal[0] = nl;
             sScal[3] = E;

@@ -26,6 +26,8 @@ constexpr int kVtab = 88;                   // per view: Cholesky factor (21) + 
 
 // <= count points of ONE view, contiguous in the point arrays
 struct Piece { int view, start, count, pad; };
+// what a persistent warp needs to start: its piece range and its first piece, in ONE 32-byte load
+struct __align__(16) WarpRec { int p0, p1, end, pad1; Piece first; };   // end: one past the chunk's last point
 
 struct LmState {
     double lam, E_cur, E_trial, sse;
@@ -43,10 +45,10 @@ struct Dev {  // everything the kernels need; passed by value
     int sc_blocks;                        // view blocks of k_schur (one more block sums A)
     const double *X, *Y, *Z, *U, *V;      // SoA detections
     const Piece* ev_piece;                // ev_pieces, in point (= view) order
-    const int* ev_chunk;                  // ev_warps + 1 : piece range of warp w
+    const WarpRec* ev_rec;                // ev_warps    : piece range (and first piece) of warp w
     const int* view_piece;                // M + 1       : piece range of view v
     const Piece* co_piece;
-    const int* co_chunk;                  // co_warps + 1
+    const WarpRec* co_rec;                // co_warps
     double* Pbuf;                         // 2 x K
     ViewC* views;                         // 2 x M
     double* partA;                        // ev_blocks x kNA
@@ -153,11 +155,12 @@ __device__ __forceinline__ void accum_BD(const PointOut<MODEL>& o, double (&acc)
 // after the view constants are in sview (warp-synchronised), `body(point)` per point of the
 // lane, `end(piece, index)` with all 32 lanes converged.
 template <class Begin, class Body, class End>
-__device__ __forceinline__ void sweep_pieces(const Dev& d, const Piece* __restrict__ pieces, int p0, int p1,
+__device__ __forceinline__ void sweep_pieces(const Dev& d, const Piece* __restrict__ pieces, const WarpRec& rec,
                                              const ViewC* __restrict__ views, ViewC& sview, int lane,
                                              Begin begin, Body body, End end) {
+    const int p0 = rec.p0, p1 = rec.p1;
     if (p0 >= p1) return;
-    Piece cur = pieces[p0];
+    Piece cur = rec.first;
     Pt pn;
     if (lane < cur.count) load_point(d, (long long)cur.start + lane, pn);
     double vn = 0.0;
@@ -192,163 +195,6 @@ __global__ void k_make_views(Dev d, int which_is_cur) {
     ViewC w;
     make_view(d.Pbuf + (long long)b * d.K + d.L + 6ll * v, w);
     d.views[(long long)b * d.M + v] = w;
-}
-
-// ---- the fused evaluation pass ----------------------------------------------------------------
-template <int MODEL>
-__global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
-    using T = ModelTraits<MODEL>;
-    constexpr int L = T::L;
-    const LmState* st = d.st;
-    if (st->done || !st->need_eval) return;
-    __shared__ double sc[16];
-    __shared__ __align__(16) ViewC sview[kBlockWarps];
-    __shared__ double sred[kBlockWarps][kNA];
-    __shared__ double sE[kBlockWarps];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int cur = st->cur;
-    const double* P = d.Pbuf + (long long)cur * d.K;
-    const ViewC* views = d.views + (long long)cur * d.M;
-    if (threadIdx.x < L) sc[threadIdx.x] = P[threadIdx.x];
-    const int w = blockIdx.x * kBlockWarps + warp;
-    int p0 = 0, p1 = 0;
-    if (w < d.ev_warps) { p0 = d.ev_chunk[w]; p1 = d.ev_chunk[w + 1]; }
-    __syncthreads();
-    // sweep 1: B_v, D_v, g_v -- one row of kNBD slots per piece
-    {
-        double acc[kNBD];
-#pragma unroll
-        for (int i = 0; i < kNBD; ++i) acc[i] = 0.0;
-        sweep_pieces(d, d.ev_piece, p0, p1, views, sview[warp], lane,
-            [&](const Piece&, int) {},
-            [&](const Pt& p) {
-                PointOut<MODEL> o;
-                point_eval<MODEL, true, true>(sc, sview[warp], p.X, p.Y, p.Z, p.U, p.V, o);
-                accum_BD<MODEL>(o, acc);
-            },
-            [&](const Piece&, int pi) {
-                warp_reduce_scatter<kNBD>(acc, lane);
-                double* row = d.partBD + (long long)pi * kNBD + lane * (kNBD / 32);
-#pragma unroll
-                for (int j = 0; j < kNBD / 32; ++j) row[j] = acc[j];
-#pragma unroll
-                for (int i = 0; i < kNBD; ++i) acc[i] = 0.0;
-            });
-    }
-    // sweep 2: A, g_c, E -- accumulated over all pieces of the warp, one row per block
-    {
-        double acc[kNA];
-#pragma unroll
-        for (int i = 0; i < kNA; ++i) acc[i] = 0.0;
-        double e = 0.0;
-        sweep_pieces(d, d.ev_piece, p0, p1, views, sview[warp], lane,
-            [&](const Piece&, int) {},
-            [&](const Pt& p) {
-                PointOut<MODEL> o;
-                point_eval<MODEL, true, false>(sc, sview[warp], p.X, p.Y, p.Z, p.U, p.V, o);
-                accum_A<MODEL>(o, acc, e);
-            },
-            [&](const Piece&, int) {});
-        warp_reduce_scatter<kNA>(acc, lane);
-        e = warp_sum(e);
-        sred[warp][2 * lane] = acc[0];
-        sred[warp][2 * lane + 1] = acc[1];
-        if (lane == 0) sE[warp] = e;
-    }
-    __syncthreads();
-    if (threadIdx.x < kNA) {
-        double s = sred[0][threadIdx.x];
-#pragma unroll
-        for (int k = 1; k < kBlockWarps; ++k) s += sred[k][threadIdx.x];
-        d.partA[(long long)blockIdx.x * kNA + threadIdx.x] = s;
-    } else if (threadIdx.x == kNA) {
-        double s = sE[0];
-#pragma unroll
-        for (int k = 1; k < kBlockWarps; ++k) s = __dadd_rn(s, sE[k]);
-        d.partE[blockIdx.x] = s;
-    }
-}
-
-// ---- accept / reject, lambda update, termination: src/calibrate.py:155-168 ------------------
-// COND: the launch sits inside the WHILE node of the whole-loop graph and sets its condition.  (Kept
-// out of the plain variants: a kernel that calls the device runtime cannot be profiled by ncu.)
-template <bool COND>
-__device__ __forceinline__ void lm_accept(const Dev& d) {
-    LmState* st = d.st;
-    const double E = st->E_cur, E1 = d.etrial[0], lam = st->lam;
-    const int it = st->iter;
-    const bool acc = E1 < E;   // strict; NaN rejects
-    double* tr = d.trace + 4ll * it;
-    tr[0] = E; tr[1] = E1; tr[2] = lam; tr[3] = acc ? 1.0 : 0.0;
-    double nl;
-    if (acc) { st->cur ^= 1; nl = lam / 10.0; st->need_eval = 1; }
-    else     { nl = lam * 10.0; st->need_eval = 0; }
-    st->lam = nl;
-    st->E_trial = E1;
-    st->sse = E;
-    st->iter = it + 1;
-    const int done = (!(st->lam_min < nl && nl < st->lam_max) || E < st->err_min || it + 1 >= st->max_iters) ? 1 : 0;
-    if (done) st->done = 1;
-    if (COND) cudaGraphSetConditional(d.cond, done ? 0u : 1u);
-}
-
-template <bool COND>
-__global__ void k_accept(Dev d) {
-    if (d.st->done) return;
-    lm_accept<COND>(d);
-}
-
-// ---- cost-only sweep at the trial point -------------------------------------------------------
-template <int MODEL, bool COND>
-__global__ void __launch_bounds__(kBlockThreads, 2) k_cost(Dev d, int fuse_accept) {
-    LmState* st = d.st;
-    if (st->done) return;
-    constexpr int L = ModelTraits<MODEL>::L;
-    __shared__ double sc[16];
-    __shared__ __align__(16) ViewC sview[kBlockWarps];
-    __shared__ double sE[kBlockWarps];
-    __shared__ int s_last;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int tb = st->cur ^ 1;
-    const double* P = d.Pbuf + (long long)tb * d.K;
-    const ViewC* views = d.views + (long long)tb * d.M;
-    if (threadIdx.x < L) sc[threadIdx.x] = P[threadIdx.x];
-    const int w = blockIdx.x * kBlockWarps + warp;
-    int p0 = 0, p1 = 0;
-    if (w < d.co_warps) { p0 = d.co_chunk[w]; p1 = d.co_chunk[w + 1]; }
-    __syncthreads();
-    double e = 0.0;
-    sweep_pieces(d, d.co_piece, p0, p1, views, sview[warp], lane,
-        [&](const Piece&, int) {},
-        [&](const Pt& p) {
-            PointOut<MODEL> o;
-            point_eval<MODEL, false, false>(sc, sview[warp], p.X, p.Y, p.Z, p.U, p.V, o);
-            e = __dadd_rn(e, fma(o.rv, o.rv, __dmul_rn(o.ru, o.ru)));
-        },
-        [&](const Piece&, int) {});
-    e = warp_sum(e);
-    if (lane == 0) sE[warp] = e;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        double s = sE[0];
-#pragma unroll
-        for (int k = 1; k < kBlockWarps; ++k) s = __dadd_rn(s, sE[k]);
-        d.partC[blockIdx.x] = s;
-        __threadfence();
-        const unsigned int prev = atomicAdd(&st->cnt_cost, 1u);
-        s_last = (prev == gridDim.x - 1);
-    }
-    __syncthreads();
-    if (!s_last) return;
-    __threadfence();
-    if (warp == 0) {
-        const double tot = warp_sum_array(d.partC, d.co_blocks, lane);
-        if (lane == 0) {
-            d.etrial[0] = tot;
-            st->cnt_cost = 0;
-            if (fuse_accept) lm_accept<COND>(d);
-        }
-    }
 }
 
 }  // namespace calib

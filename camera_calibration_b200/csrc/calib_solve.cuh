@@ -4,7 +4,7 @@
 //   dv = D_v'^-1 (g_v - B_v^T dc)                                         (6 x 6 per view)
 // with A' = A + lam diag(A), D_v' = D_v + lam diag(D_v).
 #pragma once
-#include "calib_kernels.cuh"
+#include "calib_passes.cuh"
 
 namespace calib {
 
@@ -97,17 +97,21 @@ __device__ __forceinline__ double solve_reduced_core(const double* redA, const d
     return rhs;
 }
 
-template <int MODEL>
-__device__ __forceinline__ void solve_reduced(const Dev& d, int lane) {
+// E: the cost at the current point as the evaluation pass summed it.  It seeds the loop; from the
+// second iteration on the current cost IS the trial cost of the last accepted step (set by
+// lm_accept), as in the reference where both numbers come from one function (calibrate.py:155-156).
+template <int MODEL, class Ld>
+__device__ __forceinline__ void solve_reduced(const Dev& d, const double* redA, const double* redW, double E,
+                                              int lane, Ld ld) {
     constexpr int L = ModelTraits<MODEL>::L;
     LmState* st = d.st;
-    const double dc = solve_reduced_core<MODEL>(d.red + kRedA, d.red + kRedW, st->lam, lane, LdCg());
+    const double dc = solve_reduced_core<MODEL>(redA, redW, st->lam, lane, ld);
     const int cur = st->cur;
     if (lane < L) {
         d.delta[lane] = dc;
         d.Pbuf[(long long)(cur ^ 1) * d.K + lane] = d.Pbuf[(long long)cur * d.K + lane] + dc;
     }
-    if (lane == 0) st->E_cur = __ldcg(d.red + kRedE);
+    if (lane == 0 && st->iter == 0) st->E_cur = E;
 }
 
 // ---- per-view Schur stage -------------------------------------------------------------------------
@@ -121,26 +125,11 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
     __shared__ double sv[kBlockWarps][kNBD];       // the view's summed piece rows; reused for sums
     __shared__ double sz[kBlockWarps][NZ * 6];     // Z = L^-1 [B^T | g_v], column-major by c
     __shared__ double sl[kBlockWarps][24];         // packed lower factor of the view block
+    __shared__ double sga[kBlockWarps][kNA], sredA[kNA], sredW[kNBD], sge[kBlockWarps + 1];
     __shared__ int s_last;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nvb = d.sc_blocks;
-    if ((int)blockIdx.x == nvb) {
-        // the extra block: column sums of the intrinsic-sweep rows, and the cost
-        const int col = tid & (kNA - 1), rg = tid >> 6;          // 4 row groups x 64 columns
-        double s = 0.0;
-        for (int r = rg; r < d.ev_blocks; r += 4) s += __ldcg(d.partA + (long long)r * kNA + col);
-        double (*sa)[kNA] = reinterpret_cast<double (*)[kNA]>(&sv[0][0]);
-        sa[rg][col] = s;
-        __syncthreads();
-        if (tid < kNA) d.red[kRedA + tid] = (sa[0][tid] + sa[1][tid]) + (sa[2][tid] + sa[3][tid]);
-        if (warp == 7) {
-            const double e = warp_sum_array(d.partE, d.ev_blocks, lane);
-            if (lane == 0) {
-                d.red[kRedE] = e;
-                if (st->need_eval) st->n_eval += 1;
-            }
-        }
-    } else {
+    {
         // which entries of W this lane accumulates: e = lane + 32 k  ->  (p, c), c in [p, L]
         int ep[3], ec[3];
 #pragma unroll
@@ -223,7 +212,10 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
             d.partW[(long long)blockIdx.x * kNBD + tid] = s;
         }
     }
-    // the last block to finish sums the block rows of W in a fixed order
+    // The last block to finish gathers, in one round trip and in a fixed order, the block rows of W,
+    // the block rows of the intrinsic sweep (A, g_c) and the block costs; it publishes the reduced
+    // system (red[], all-reduced when the views are sharded) and, on one GPU, solves it from
+    // shared memory straight away.
     __threadfence();
     __syncthreads();
     if (tid == 0) {
@@ -233,27 +225,50 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
     __syncthreads();
     if (!s_last) return;
     __threadfence();
-    {   // rows r = warp, warp + 8, ...; three columns per lane; then the eight warps in order
-        double s0 = 0.0, s1 = 0.0, s2 = 0.0;
+    {
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0, a0 = 0.0, a1 = 0.0, e = 0.0;
 #pragma unroll 4
         for (int r = warp; r < nvb; r += kBlockWarps) {
             const double* row = d.partW + (long long)r * kNBD;
             s0 += __ldcg(row + lane); s1 += __ldcg(row + lane + 32); s2 += __ldcg(row + lane + 64);
         }
+#pragma unroll 4
+        for (int r = warp; r < d.ev_blocks; r += kBlockWarps) {
+            const double* row = d.partA + (long long)r * kNA;
+            a0 += __ldcg(row + lane); a1 += __ldcg(row + lane + 32);
+        }
+        for (int r = tid; r < d.ev_blocks; r += kBlockThreads) e = __dadd_rn(e, __ldcg(d.partE + r));
+        e = warp_sum(e);
         sv[warp][lane] = s0; sv[warp][lane + 32] = s1; sv[warp][lane + 64] = s2;
+        sga[warp][lane] = a0; sga[warp][lane + 32] = a1;
+        if (lane == 0) sge[warp] = e;
     }
     __syncthreads();
     if (tid < kNBD) {
         double s = sv[0][tid];
 #pragma unroll
         for (int k = 1; k < kBlockWarps; ++k) s += sv[k][tid];
+        sredW[tid] = s;
         d.red[kRedW + tid] = s;
+    } else if (tid < kNBD + kNA) {
+        const int c = tid - kNBD;
+        double s = sga[0][c];
+#pragma unroll
+        for (int k = 1; k < kBlockWarps; ++k) s += sga[k][c];
+        sredA[c] = s;
+        d.red[kRedA + c] = s;
+    } else if (tid == kNBD + kNA) {
+        double s = sge[0];
+#pragma unroll
+        for (int k = 1; k < kBlockWarps; ++k) s = __dadd_rn(s, sge[k]);
+        sge[kBlockWarps] = s;
+        d.red[kRedE] = s;
+        st->cnt_schur = 0;
+        if (st->need_eval) st->n_eval += 1;
     }
-    if (tid == 0) st->cnt_schur = 0;
     if (fuse_solve) {
-        __threadfence();
         __syncthreads();
-        if (warp == 0) solve_reduced<MODEL>(d, lane);
+        if (warp == 0) solve_reduced<MODEL>(d, sredA, sredW, sge[kBlockWarps], lane, LdPlain());
     }
 }
 
@@ -261,7 +276,7 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
 template <int MODEL>
 __global__ void k_solve(Dev d) {
     if (d.st->done) return;
-    solve_reduced<MODEL>(d, threadIdx.x);
+    solve_reduced<MODEL>(d, d.red + kRedA, d.red + kRedW, __ldcg(d.red + kRedE), threadIdx.x, LdCg());
 }
 
 // ---- back-substitution, trial parameters and trial view constants: one warp per view -------------

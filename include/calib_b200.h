@@ -69,6 +69,11 @@ int calib_set_segment(calib_t* h, int points_per_task);
  * views are sharded (the body then holds NCCL nodes). */
 int calib_set_loop_mode(calib_t* h, int mode);
 
+/* How the trial-cost sweep brings the detections in: 1 = bulk copies (TMA) into a per-warp
+ * shared-memory ring, 0 = coalesced loads with register prefetch, -1 (default) = by size (the ring
+ * when the detections exceed what L2 keeps between sweeps).  Results are bit-identical. */
+int calib_set_cost_staging(calib_t* h, int mode);
+
 /* Page-locked host memory for detections / parameters handed to calib_create / calib_lm_run
  * (optional: any host pointer works, pinned ones copy at full PCIe rate).  NULL on failure. */
 void* calib_host_alloc(size_t bytes);
@@ -121,6 +126,14 @@ int calib_set_profiling(calib_t* h, int on);
  * 2 = back-substitution (k_backsub), 3 = cost sweep (k_cost), 4 = reduced solve as its own
  * launch (sharded views only).  Sums over the last run. */
 int calib_kernel_time(const calib_t* h, int which, double* total_ms, int64_t* launches);
+
+/* Average device time (microseconds) of one kernel of the iteration at P with damping lam:
+ * which 0 = k_eval, 1 = k_schur (+ reduced solve), 2 = k_backsub, 3 = k_cost; `reps` launches
+ * back to back between two CUDA events on the handle's stream.  flush = 0: detections stay in L2
+ * between launches, as between the iterations of a run; flush = 1: 256 MB L2 flush before every
+ * launch (its own time subtracted).  This is what bench.py's roofline divides by. */
+int calib_time_kernel(calib_t* h, const double* P, double lam, int which, int reps, int flush,
+                      double* avg_us);
 
 /* Micro-benchmarks used for the roofline denominators (FP64 FMA pipe; device copy). */
 int calib_measure_fp64_peak(int device_id, double* tflops);

@@ -488,25 +488,18 @@ def main():
                              "api": "Calibrator.refineCalibrationParameters(A, W, k, allDetections, maxIters): "
                                     "list of per-view arrays in, (sse, A, W, k) out"}
 
-    # ---- roofline of the dominant kernel (k_eval): events around every launch, separate run
+    # ---- roofline of the dominant kernel (k_eval): CUDA events around back-to-back launches on the
+    # library's stream (calib_time_kernel), L2-warm as between the iterations of a run, and after
+    # an L2 flush before every launch
     roof = None
     kt = {}
-    prob.set_profiling(True)
-    prob.upload(Ploc)
-    prob.flush_l2()
-    prob.lm_run_resident(MAX_ITERS)
-    _, _, ev_prof = prob.last_run_stats()
-    for i, nm in enumerate(["k_eval", "k_schur", "k_backsub", "k_cost", "k_solve"]):
-        ms_k, n_k = prob.kernel_time(i)
-        if n_k:
-            kt[nm] = {"launches": n_k, "total_us": 1e3 * ms_k}
-    prob.set_profiling(False)
+    for i, nm in enumerate(["k_eval", "k_schur", "k_backsub", "k_cost"]):
+        kt[nm] = {"us_l2_warm": prob.time_kernel(Ploc, i, 30), "us_after_l2_flush": prob.time_kernel(Ploc, i, 10, flush=True)}
     if rank == 0:
         peak64 = cc.calibrate.fp64_peak_tflops(local)
         n_loc = int(offs[-1])
-        # launches after a rejected step return at once; the measured time belongs to the launches
-        # that evaluated (their number = Jacobian passes of the profiled run)
-        avg_s = 1e-6 * kt["k_eval"]["total_us"] / max(ev_prof, 1)
+        avg_s = 1e-6 * kt["k_eval"]["us_l2_warm"]
+        cold_s = 1e-6 * kt["k_eval"]["us_after_l2_flush"]
         fl = FLOPS_PER_POINT[model] * n_loc
         by = 2 * BYTES_PER_POINT * n_loc          # two sweeps over the detections
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(
@@ -517,9 +510,11 @@ def main():
                 "peak_source": "DFMA micro-benchmark in this run (calib_measure_fp64_peak): FP64 is not in "
                                "MEASURED_PEAKS.json and the kernel is FP64-pipe bound, not HBM bound",
                 "flops_per_point": FLOPS_PER_POINT[model], "points_per_launch": n_loc,
-                "avg_launch_us": avg_s * 1e6, "timed_launches": int(ev_prof),
-                "hbm": {"achieved": by / avg_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                        "frac": by / avg_s / 1e9 / hbm_peak, "bytes_per_point_per_sweep": BYTES_PER_POINT,
+                "avg_launch_us": avg_s * 1e6, "avg_launch_us_after_l2_flush": cold_s * 1e6,
+                "frac_after_l2_flush": fl / cold_s / 1e12 / peak64,
+                "fp64_pipe_active_pct_ncu": "see profiles/README.md (ncu sm__inst_executed_pipe_fp64)",
+                "hbm": {"achieved": by / cold_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                        "frac": by / cold_s / 1e9 / hbm_peak, "bytes_per_point_per_sweep": BYTES_PER_POINT,
                         "peak_source": "MEASURED_PEAKS.json (of measured)" if peaks else "fallback 6650 (of fallback)"}}
 
     cpu = None

@@ -371,6 +371,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--problems", type=int, default=8192)
     ap.add_argument("--cpu-sample", type=int, default=512)
+    ap.add_argument("--transport", default="auto", choices=["auto", "peer", "nccl"],
+                    help="sharded views: in-kernel all-reduce over NVLink peer memory, or NCCL all-reduces")
     args = ap.parse_args()
     if args.workload == "cfg4":
         if args.steps == 100:
@@ -405,12 +407,10 @@ def main():
         prob.set_segment(args.segment)
     if args.loop_mode:
         prob.set_loop_mode(args.loop_mode)
+    transport = "none"
     if world > 1:
-        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
-        if rank == 0:
-            idt = torch.frombuffer(bytearray(cc.calibrate.comm_unique_id()), dtype=torch.uint8).cuda()
-        dist.broadcast(idt, 0)
-        prob.comm_init(world, rank, bytes(idt.cpu().numpy().tobytes()))
+        from camera_calibration_b200 import sharding
+        transport = sharding.connect(prob, dist, args.transport)
 
     def barrier():
         torch.cuda.synchronize()
@@ -526,7 +526,10 @@ def main():
             "metric": "lm_iterations_per_sec", "value": value, "unit": "LM iterations/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot_ms / args.steps,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic", "config": workload_config(args, c, offs_all),
+            "data": "synthetic", "config": dict(workload_config(args, c, offs_all), exchange={
+                "none": "none (one GPU)",
+                "peer": "reduced system (161 doubles) + trial cost summed inside k_schur / k_cost through NVLink peer memory",
+                "nccl": "two ncclAllReduce per iteration (161 doubles, 1 double)"}[transport]),
             "jacobian_rows_per_sec": rows_per_s, "lm_iterations_per_step": tot_it / args.steps,
             "jacobian_passes_per_step": tot_eval / args.steps, "final_sse": sse,
             "wall_ms_per_step_incl_flush": 1e3 * t_wall / args.steps,

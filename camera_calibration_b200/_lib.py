@@ -110,6 +110,10 @@ def lib():
         "calib_comm_unique_id": (c_int, [_vp]),
         "calib_comm_init": (c_int, [_vp, c_int, c_int, _vp]),
         "calib_comm_share": (c_int, [_vp, _vp]),
+        "calib_peer_export": (c_int, [_vp, _vp]),
+        "calib_peer_attach": (c_int, [_vp, c_int, c_int, _vp]),
+        "calib_set_transport": (c_int, [_vp, c_int]),
+        "calib_transport": (c_int, [_vp]),
         "calib_batch_create": (c_int, [ctypes.POINTER(_vp), c_int, c_i64, _i64, _i64, _d, _d, c_int]),
         "calib_batch_destroy": (None, [_vp]),
         "calib_batch_last_error": (ctypes.c_char_p, [_vp]),

@@ -253,6 +253,24 @@ class Problem:
     def comm_share(self, owner):
         self._check(self._L.calib_comm_share(self._h, owner._h))
 
+    def peer_export(self) -> bytes:
+        """64-byte CUDA IPC handle of this rank's inbox for the in-kernel all-reduce"""
+        buf = ctypes.create_string_buffer(64)
+        self._check(self._L.calib_peer_export(self._h, ctypes.cast(buf, ctypes.c_void_p)))
+        return buf.raw
+
+    def peer_attach(self, nranks, rank, handles: bytes):
+        assert len(handles) == 64 * nranks
+        buf = ctypes.create_string_buffer(handles, len(handles))
+        self._check(self._L.calib_peer_attach(self._h, int(nranks), int(rank), ctypes.cast(buf, ctypes.c_void_p)))
+
+    def set_transport(self, mode):
+        """0 automatic, 1 NCCL all-reduces, 2 in-kernel exchange over NVLink peer memory"""
+        self._check(self._L.calib_set_transport(self._h, int(mode)))
+
+    def transport(self):
+        return int(self._L.calib_transport(self._h))
+
 
 class BatchProblem:
     """A batch of independent calibrations resident on one GPU (calib_batch_t): one thread block

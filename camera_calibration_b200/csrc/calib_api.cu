@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -33,6 +34,23 @@ static void free_pool(std::vector<void*>& pool) {
     for (void* p : pool) cudaFree(p);
     pool.clear();
 }
+
+// Inbox of this rank for the in-kernel all-reduce (calib_peer.cuh) and the peers' inboxes as mapped
+// into this process (CUDA IPC).  Owned by the handle that exported it, borrowed by calib_comm_share.
+struct PeerComm {
+    int nranks = 1, rank = 0, device = 0;
+    uint4* inbox = nullptr;                  // cudaMalloc: kPeerInboxBytes, then the counters
+    void* mapped[kPeerMaxRanks] = {};        // peers' inboxes (cudaIpcOpenMemHandle)
+    ~PeerComm() {
+        cudaSetDevice(device);
+        for (void* m : mapped) if (m) cudaIpcCloseMemHandle(m);
+        if (inbox) cudaFree(inbox);
+    }
+    bool mapped_ok() const {
+        for (int r = 0; r < nranks; ++r) if (r != rank && !mapped[r]) return false;
+        return true;
+    }
+};
 
 struct calib_handle {
     int model = 0, L = 0, device = 0, n_sm = 148;
@@ -63,6 +81,8 @@ struct calib_handle {
     ncclComm_t comm = nullptr;
     bool comm_owned = false;
     int nranks = 1, rank = 0;
+    std::shared_ptr<PeerComm> peer;        // in-kernel exchange over NVLink peer memory
+    int transport = 0;                     // 0 auto (peer memory when attached, else NCCL), 1 NCCL, 2 peer memory
     double* l2buf = nullptr;
     size_t l2bytes = 0;
 };
@@ -521,20 +541,28 @@ void enqueue_cost(calib_handle* h, Launcher& ln, int fuse_accept) {
     ln.count += 1;
 }
 
-// one LM iteration: src/calibrate.py:144-168
+bool peer_active(const calib_handle* h) {
+    return h->peer && h->peer->nranks > 1 && h->peer->mapped_ok() && h->transport != 1;
+}
+bool nccl_active(const calib_handle* h) { return h->comm && !peer_active(h); }
+
+// one LM iteration: src/calibrate.py:144-168.  Sharded views: the reduced system and the trial cost
+// are summed over the ranks either inside k_schur / k_cost through peer memory (4 launches, as on one
+// GPU) or by two NCCL all-reduces, each followed by a small kernel that consumes the sum.
 template <int MODEL>
 int enqueue_iteration(calib_handle* h, Launcher& ln) {
     const Dev& d = h->dev;
+    const bool nccl = nccl_active(h);
     enqueue_eval<MODEL>(h, ln);
-    enqueue_schur<MODEL>(h, ln, h->comm ? 0 : 1);
-    if (h->comm) {
+    enqueue_schur<MODEL>(h, ln, nccl ? 0 : 1);
+    if (nccl) {
         if (g_nccl.AllReduce(d.red, d.red, kRedN, ncclDouble, ncclSum, h->comm, h->stream) != ncclSuccess)
             return fail(h, CALIB_E_COMM, "ncclAllReduce(reduced system) failed");
         enqueue_solve<MODEL>(h, ln);
     }
     enqueue_backsub<MODEL>(h, ln);
-    enqueue_cost<MODEL>(h, ln, h->comm ? 0 : 1);
-    if (h->comm) {
+    enqueue_cost<MODEL>(h, ln, nccl ? 0 : 1);
+    if (nccl) {
         if (g_nccl.AllReduce(d.etrial, d.etrial, 1, ncclDouble, ncclSum, h->comm, h->stream) != ncclSuccess)
             return fail(h, CALIB_E_COMM, "ncclAllReduce(trial cost) failed");
         if (d.use_cond) k_accept<true><<<1, 1, 0, h->stream>>>(d);
@@ -548,7 +576,19 @@ int enqueue_iteration_any(calib_handle* h, Launcher& ln) {
     return h->model == 0 ? enqueue_iteration<0>(h, ln) : enqueue_iteration<1>(h, ln);
 }
 
-int kernels_per_iteration(const calib_handle* h) { return h->comm ? 6 : 4; }
+int kernels_per_iteration(const calib_handle* h) { return nccl_active(h) ? 6 : 4; }
+
+// fills / clears the device view of the peer communicator according to the chosen transport
+void apply_transport(calib_handle* h) {
+    drop_graph(h);
+    PeerDev& p = h->dev.peer;
+    memset(&p, 0, sizeof p);
+    if (!peer_active(h)) return;
+    const PeerComm& c = *h->peer;
+    p.nranks = c.nranks; p.rank = c.rank;
+    for (int r = 0; r < c.nranks; ++r) p.box[r] = r == c.rank ? c.inbox : (uint4*)c.mapped[r];
+    p.seq = reinterpret_cast<unsigned int*>(c.inbox + kPeerInboxElems);
+}
 
 // host-driven loop: one iteration as a graph
 int build_graph(calib_handle* h) {
@@ -678,7 +718,10 @@ extern "C" int calib_lm_run_resident(calib_t* h, int maxIters, double lam0, doub
     const bool prof = h->profiling;
     // the device-driven loop needs every node of the body on this GPU; with a communicator the
     // loop is host-driven unless asked for explicitly
-    const bool device_loop = !prof && (h->loop_mode == 2 || (h->loop_mode == 0 && !h->comm));
+    if (h->loop_mode == 2 && nccl_active(h))
+        return fail(h, CALIB_E_STATE, "loop mode 2: a WHILE-node body cannot hold NCCL nodes (cudaGraphInstantiate rejects "
+                                      "them); use the peer-memory transport (calib_peer_attach) or loop mode 1");
+    const bool device_loop = !prof && (h->loop_mode == 2 || (h->loop_mode == 0 && !nccl_active(h)));
     if (!prof) RC(device_loop ? build_loop_graph(h) : build_graph(h));
     for (auto& pe : h->prof_events) { cudaEventDestroy(pe.second.first); cudaEventDestroy(pe.second.second); }
     h->prof_events.clear();
@@ -727,6 +770,8 @@ extern "C" int calib_lm_run_resident(calib_t* h, int maxIters, double lam0, doub
     }
     if (sse_out) *sse_out = h->h_state->sse;
     if (iters_out) *iters_out = h->h_state->iter;
+    if (h->h_state->comm_fail)
+        return fail(h, CALIB_E_COMM, "a peer rank never arrived at the in-kernel all-reduce (timeout)");
     return CALIB_OK;
 }
 
@@ -814,7 +859,7 @@ int eval_system(calib_handle* h, const double* P, double lam, bool solve) {
     Launcher ln{h, false};
     if (h->model == 0) { enqueue_eval<0>(h, ln); enqueue_schur<0>(h, ln, 0); }
     else { enqueue_eval<1>(h, ln); enqueue_schur<1>(h, ln, 0); }
-    if (h->comm && g_nccl.AllReduce(h->dev.red, h->dev.red, kRedN, ncclDouble, ncclSum, h->comm, h->stream) != ncclSuccess)
+    if (nccl_active(h) && g_nccl.AllReduce(h->dev.red, h->dev.red, kRedN, ncclDouble, ncclSum, h->comm, h->stream) != ncclSuccess)
         return fail(h, CALIB_E_COMM, "ncclAllReduce failed");
     if (solve) {
         if (h->model == 0) { enqueue_solve<0>(h, ln); enqueue_backsub<0>(h, ln); }
@@ -843,7 +888,7 @@ extern "C" int calib_cost(calib_t* h, const double* P, double* E) {
     RC(make_views(h, 0));
     Launcher ln{h, false};
     if (h->model == 0) enqueue_cost<0>(h, ln, 0); else enqueue_cost<1>(h, ln, 0);
-    if (h->comm && g_nccl.AllReduce(h->dev.etrial, h->dev.etrial, 1, ncclDouble, ncclSum, h->comm, h->stream) != ncclSuccess)
+    if (nccl_active(h) && g_nccl.AllReduce(h->dev.etrial, h->dev.etrial, 1, ncclDouble, ncclSum, h->comm, h->stream) != ncclSuccess)
         return fail(h, CALIB_E_COMM, "ncclAllReduce failed");
     CUDA_TRY(h, cudaMemcpyAsync(h->h_pinned, h->dev.etrial, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     RC(sync(h));
@@ -1003,6 +1048,7 @@ extern "C" int calib_comm_init(calib_t* h, int nranks, int rank, const void* id1
         return fail(h, CALIB_E_COMM, g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "ncclCommInitRank failed");
     }
     h->comm_owned = true;
+    apply_transport(h);
     return CALIB_OK;
 }
 
@@ -1014,7 +1060,73 @@ extern "C" int calib_comm_share(calib_t* h, const calib_t* owner) {
     if (h->comm && h->comm_owned) g_nccl.CommDestroy(h->comm);
     h->comm = owner->comm; h->comm_owned = false;
     h->nranks = owner->nranks; h->rank = owner->rank;
+    h->peer = owner->peer; h->transport = owner->transport;
+    apply_transport(h);
     return CALIB_OK;
+}
+
+// ---- in-kernel all-reduce over NVLink peer memory (calib_peer.cuh) -------------------------------------
+extern "C" int calib_peer_export(calib_t* h, void* handle64) {
+    RC(check_handle(h));
+    if (!handle64) return fail(h, CALIB_E_ARG, "calib_peer_export: handle64 is NULL");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    if (!h->peer || h->peer->nranks > 1) {   // (re-)export: a fresh inbox, sequence numbers start over
+        auto pc = std::make_shared<PeerComm>();
+        pc->device = h->device;
+        const size_t bytes = kPeerInboxBytes + 64;
+        CUDA_TRY(h, cudaMalloc((void**)&pc->inbox, bytes));
+        CUDA_TRY(h, cudaMemset(pc->inbox, 0, bytes));
+        CUDA_TRY(h, cudaDeviceSynchronize());
+        h->peer = pc;
+        apply_transport(h);
+    }
+    cudaIpcMemHandle_t mh;
+    CUDA_TRY(h, cudaIpcGetMemHandle(&mh, h->peer->inbox));
+    memcpy(handle64, &mh, 64);
+    return CALIB_OK;
+}
+
+extern "C" int calib_peer_attach(calib_t* h, int nranks, int rank, const void* handles) {
+    RC(check_handle(h));
+    if (!handles || nranks < 1 || nranks > kPeerMaxRanks || rank < 0 || rank >= nranks)
+        return fail(h, CALIB_E_ARG, "calib_peer_attach: bad args (at most 8 ranks)");
+    if (!h->peer || !h->peer->inbox) return fail(h, CALIB_E_STATE, "calib_peer_attach: call calib_peer_export first");
+    PeerComm& pc = *h->peer;
+    for (void*& m : pc.mapped) if (m) { cudaIpcCloseMemHandle(m); m = nullptr; }
+    pc.nranks = nranks; pc.rank = rank;
+    for (int r = 0; r < nranks; ++r) {
+        if (r == rank) continue;
+        cudaIpcMemHandle_t mh;
+        memcpy(&mh, (const char*)handles + 64 * (size_t)r, 64);
+        cudaError_t e = cudaIpcOpenMemHandle(&pc.mapped[r], mh, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            pc.mapped[r] = nullptr;
+            pc.nranks = 1;
+            cudaGetLastError();
+            apply_transport(h);
+            char b[256];
+            snprintf(b, sizeof b, "calib_peer_attach: cudaIpcOpenMemHandle(rank %d) failed: %s", r, cudaGetErrorString(e));
+            return fail(h, CALIB_E_COMM, b);
+        }
+    }
+    h->nranks = nranks; h->rank = rank;
+    apply_transport(h);
+    return CALIB_OK;
+}
+
+extern "C" int calib_set_transport(calib_t* h, int mode) {
+    if (!h) return fail(nullptr, CALIB_E_ARG, "NULL handle");
+    if (mode < 0 || mode > 2) return fail(h, CALIB_E_ARG, "calib_set_transport: 0 auto, 1 NCCL, 2 peer memory");
+    if (mode == 2 && !(h->peer && h->peer->nranks > 1 && h->peer->mapped_ok()))
+        return fail(h, CALIB_E_STATE, "calib_set_transport: no peer communicator attached");
+    h->transport = mode;
+    apply_transport(h);
+    return CALIB_OK;
+}
+
+extern "C" int calib_transport(const calib_t* h) {
+    if (!h) return -1;
+    return peer_active(h) ? 2 : (h->comm ? 1 : 0);
 }
 
 // ---- batch of independent calibrations (calib_batch.cuh) -------------------------------------------

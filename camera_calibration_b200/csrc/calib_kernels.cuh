@@ -14,6 +14,7 @@
 // Replaces the loop body of src/calibrate.py:143-168 (see include/calib_b200.h).
 #pragma once
 #include "calib_device.cuh"
+#include "calib_peer.cuh"
 
 namespace calib {
 
@@ -33,6 +34,7 @@ struct LmState {
     double lam, E_cur, E_trial, sse;
     double lam_min, lam_max, err_min;
     int iter, max_iters, done, need_eval, cur, nranks;
+    int comm_fail, pad0;   // comm_fail: a peer never arrived at an exchange (calib_peer.cuh)
     unsigned int cnt_schur, cnt_cost;
     long long n_eval;   // Jacobian evaluations actually executed
 };
@@ -64,6 +66,7 @@ struct Dev {  // everything the kernels need; passed by value
     LmState* st;
     cudaGraphConditionalHandle cond;      // WHILE node of the whole-loop graph
     int use_cond;
+    PeerDev peer;                         // nranks > 1: the kernels all-reduce over peer memory
 };
 
 // ---- slot layouts ---------------------------------------------------------------------------

@@ -144,10 +144,14 @@ __global__ void __launch_bounds__(kBlockThreads, 2) k_cost(Dev d, int fuse_accep
     rec.p0 = rec.p1 = 0;
     if (w < d.co_warps) rec = d.co_rec[w];
     LmState* st = d.st;
-    if (st->done) return;
+    if (st->done) {   // also after a failed exchange: the WHILE node must not spin
+        if (COND) { if (blockIdx.x == 0 && threadIdx.x == 0) cudaGraphSetConditional(d.cond, 0u); }
+        return;
+    }
     __shared__ double sc[16];
     __shared__ __align__(16) ViewC sview[kBlockWarps];
     __shared__ double sE[kBlockWarps];
+    __shared__ double s_tot;
     __shared__ int s_last;
     __shared__ __align__(8) unsigned long long bars[kBlockWarps][kCostStages];
     const int tb = st->cur ^ 1;
@@ -181,10 +185,19 @@ __global__ void __launch_bounds__(kBlockThreads, 2) k_cost(Dev d, int fuse_accep
     __threadfence();
     if (warp == 0) {
         const double tot = warp_sum_array(d.partC, d.co_blocks, lane);
-        if (lane == 0) {
-            d.etrial[0] = tot;
-            st->cnt_cost = 0;
-            if (fuse_accept) lm_accept<COND>(d);
+        if (lane == 0) s_tot = tot;
+    }
+    __syncthreads();
+    bool ok = true;
+    if (d.peer.nranks > 1) ok = peer_allreduce(d.peer, 1, &s_tot, 1, &s_last);   // views sharded: sum over the ranks
+    if (threadIdx.x == 0) {
+        d.etrial[0] = s_tot;
+        st->cnt_cost = 0;
+        if (!ok) {
+            st->comm_fail = 1; st->done = 1;
+            if (COND) cudaGraphSetConditional(d.cond, 0u);
+        } else if (fuse_accept) {
+            lm_accept<COND>(d);
         }
     }
 }

@@ -125,7 +125,8 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
     __shared__ double sv[kBlockWarps][kNBD];       // the view's summed piece rows; reused for sums
     __shared__ double sz[kBlockWarps][NZ * 6];     // Z = L^-1 [B^T | g_v], column-major by c
     __shared__ double sl[kBlockWarps][24];         // packed lower factor of the view block
-    __shared__ double sga[kBlockWarps][kNA], sredA[kNA], sredW[kNBD], sge[kBlockWarps + 1];
+    __shared__ double sga[kBlockWarps][kNA], sge[kBlockWarps];
+    __shared__ double sred[kPeerSlot];             // the reduced system in the layout of red[]
     __shared__ int s_last;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nvb = d.sc_blocks;
@@ -248,28 +249,30 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
         double s = sv[0][tid];
 #pragma unroll
         for (int k = 1; k < kBlockWarps; ++k) s += sv[k][tid];
-        sredW[tid] = s;
-        d.red[kRedW + tid] = s;
+        sred[kRedW + tid] = s;
     } else if (tid < kNBD + kNA) {
         const int c = tid - kNBD;
         double s = sga[0][c];
 #pragma unroll
         for (int k = 1; k < kBlockWarps; ++k) s += sga[k][c];
-        sredA[c] = s;
-        d.red[kRedA + c] = s;
+        sred[kRedA + c] = s;
     } else if (tid == kNBD + kNA) {
         double s = sge[0];
 #pragma unroll
         for (int k = 1; k < kBlockWarps; ++k) s = __dadd_rn(s, sge[k]);
-        sge[kBlockWarps] = s;
-        d.red[kRedE] = s;
+        sred[kRedE] = s;
         st->cnt_schur = 0;
         if (st->need_eval) st->n_eval += 1;
     }
-    if (fuse_solve) {
-        __syncthreads();
-        if (warp == 0) solve_reduced<MODEL>(d, sredA, sredW, sge[kBlockWarps], lane, LdPlain());
+    __syncthreads();
+    // views sharded over the GPUs of the node: sum the reduced systems of all ranks, right here
+    if (d.peer.nranks > 1 && !peer_allreduce(d.peer, 0, sred, kRedN, &s_last)) {
+        if (tid == 0) { st->comm_fail = 1; st->done = 1; }
+        return;
     }
+    if (tid < kRedN) d.red[tid] = sred[tid];
+    if (fuse_solve && warp == 0)
+        solve_reduced<MODEL>(d, sred + kRedA, sred + kRedW, sred[kRedE], lane, LdPlain());
 }
 
 // reduced solve as its own launch (after the all-reduce when the views are sharded)

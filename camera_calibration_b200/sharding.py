@@ -47,3 +47,43 @@ def allreduce_reduced_system(local_S, local_s, local_E, dist, group=None):
     out = flat.numpy()
     n = np.asarray(local_s).size
     return out[:n * n].reshape(n, n), out[n * n:n * n + n], float(out[-1])
+
+
+def connect(prob, dist, transport="auto"):
+    """Joins the ranks of `dist` (an initialised torch.distributed) for a view-sharded Problem.
+    transport "peer": in-kernel all-reduce through NVLink peer memory (CUDA IPC handles gathered
+    over `dist`); "nccl": library all-reduces; "auto": peer memory if every rank can map every
+    inbox, else NCCL.  Returns the transport in use ("peer" | "nccl" | "none")."""
+    import torch
+    world, rank = dist.get_world_size(), dist.get_rank()
+    if world == 1:
+        return "none"
+    from . import calibrate
+    dev = torch.device("cuda", torch.cuda.current_device())
+    got_peer = False
+    if transport in ("auto", "peer") and world <= 8:
+        mine = torch.frombuffer(bytearray(prob.peer_export()), dtype=torch.uint8).to(dev)
+        allh = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allh, mine)
+        ok = 1
+        try:
+            prob.peer_attach(world, rank, b"".join(bytes(t.cpu().numpy().tobytes()) for t in allh))
+        except Exception:
+            if transport == "peer":
+                raise
+            ok = 0
+        flag = torch.tensor([ok], dtype=torch.int32, device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        got_peer = bool(flag.item())
+    if got_peer and transport != "nccl":
+        prob.set_transport(2)
+        return "peer"
+    if transport == "peer":
+        raise RuntimeError("peer-memory transport not available on every rank")
+    idt = torch.zeros(128, dtype=torch.uint8, device=dev)
+    if rank == 0:
+        idt = torch.frombuffer(bytearray(calibrate.comm_unique_id()), dtype=torch.uint8).to(dev)
+    dist.broadcast(idt, 0)
+    prob.comm_init(world, rank, bytes(idt.cpu().numpy().tobytes()))
+    prob.set_transport(1)
+    return "nccl"

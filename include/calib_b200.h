@@ -65,8 +65,9 @@ int calib_set_segment(calib_t* h, int points_per_task);
 /* How the LM loop (src/calibrate.py:143-168) is driven.  2: one CUDA graph whose WHILE node
  * repeats the iteration until the device-side accept step clears the condition -- a whole
  * refinement is one launch and one read-back.  1: the host launches iteration graphs in small
- * batches and looks at the device state between them.  0 (default): 2 on one GPU, 1 when the
- * views are sharded (the body then holds NCCL nodes). */
+ * batches and looks at the device state between them.  0 (default): 2 on one GPU and with the
+ * peer-memory transport, 1 with NCCL (a WHILE body cannot hold NCCL nodes: 2 then fails with
+ * CALIB_E_STATE). */
 int calib_set_loop_mode(calib_t* h, int mode);
 
 /* How the trial-cost sweep brings the detections in: 1 = bulk copies (TMA) into a per-warp
@@ -148,6 +149,24 @@ int calib_comm_init(calib_t* h, int nranks, int rank, const void* id128);
 /* Borrow the communicator of another handle of this process (it must outlive h): lets a
  * long-lived communicator serve one calib_create/calib_lm_run/calib_destroy per calibration. */
 int calib_comm_share(calib_t* h, const calib_t* owner);
+
+/* The same exchange WITHOUT a library collective: the last thread block of the Schur kernel / the
+ * cost kernel writes its 161-double reduced system (resp. the scalar trial cost) straight into every
+ * peer's inbox through the NVLink mapping of peer memory, waits for the peers' flags and sums in rank
+ * order (bit-identical on all ranks).  The iteration keeps its four launches and the whole LM loop
+ * stays one WHILE-node graph launch per rank.  At most 8 ranks, all on one node.
+ *   calib_peer_export : allocates this rank's inbox and returns its 64-byte CUDA IPC handle;
+ *   (the host all-gathers the handles, e.g. with torch.distributed)
+ *   calib_peer_attach : maps the peers' inboxes; handles = nranks x 64 bytes, in rank order.
+ * Every rank must then make the same sequence of calib_* compute calls (each exchange is a
+ * rendezvous); a rank that never arrives makes the others return CALIB_E_COMM after a timeout.
+ * Keep the exporting handle alive until all ranks are done (a host barrier before calib_destroy).
+ * calib_comm_share also lends the peer communicator. */
+int calib_peer_export(calib_t* h, void* handle64);
+int calib_peer_attach(calib_t* h, int nranks, int rank, const void* handles);
+/* 0 = automatic (peer memory when attached, else NCCL), 1 = NCCL, 2 = peer memory. */
+int calib_set_transport(calib_t* h, int mode);
+int calib_transport(const calib_t* h);   /* in use: 0 none (one GPU), 1 NCCL, 2 peer memory */
 
 /* Batch of independent calibrations (a Python `for` over refineCalibrationParameters calls in the
  * reference; BASELINE config 4): one thread block per problem, the whole LM loop in one launch,

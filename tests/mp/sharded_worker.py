@@ -28,16 +28,17 @@ def main():
     offs, mp, sp = cc.flatten_detections(c["dets"][lo:hi])
     prob = cc.Problem(model, offs, mp, sp, device=local)
     prob.set_loop_mode(loop_mode)
-    idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
-    if rank == 0:
-        idt = torch.frombuffer(bytearray(cc.calibrate.comm_unique_id()), dtype=torch.uint8).cuda()
-    dist.broadcast(idt, 0)
-    prob.comm_init(world, rank, bytes(idt.cpu().numpy().tobytes()))
+    transport = sys.argv[4] if len(sys.argv) > 4 else "nccl"
+    used = sharding.connect(prob, dist, transport)
+    assert used == transport, (used, transport)
     sse, P, iters, tr = prob.lm_run(Ploc, 100)
+    launches = prob.last_run_stats()[1]
+    # a second run on the same communicator (sequence numbers carry on) must repeat the first bit for bit
+    sse2, P2, iters2, tr2 = prob.lm_run(Ploc, 100)
+    assert iters2 == iters and sse2 == sse and np.array_equal(P2, P) and np.array_equal(tr2, tr)
     # gather the extrinsics of every rank on rank 0
     parts = [None] * world
     dist.all_gather_object(parts, (lo, hi, P.tolist(), sse, iters, tr.tolist()))
-    prob.close()
     ok, msg = True, ""
     if rank == 0:
         Pfull = sharding.merge_params([(a, b, np.array(p)) for a, b, p, *_ in parts], L, len(c["dets"]))
@@ -61,8 +62,10 @@ def main():
         if rel > 1e-6 or abs(sse - s1) > 1e-9 * s1:
             ok, msg = False, f"parameters differ: {rel}"
         print(json.dumps({"ok": ok, "msg": msg, "world": world, "iters_sharded": iters, "iters_single": i1,
-                          "pre_plateau_iterations": int(stop), "max_rel_param_diff": rel}), flush=True)
-    dist.barrier()
+                          "pre_plateau_iterations": int(stop), "max_rel_param_diff": rel,
+                          "transport": used, "launches": int(launches)}), flush=True)
+    dist.barrier()      # nobody unmaps an inbox a peer may still write to
+    prob.close()
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)
 

@@ -371,6 +371,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--problems", type=int, default=8192)
     ap.add_argument("--cpu-sample", type=int, default=512)
+    ap.add_argument("--ladder", type=int, default=4, choices=[1, 2, 4],
+                    help="damping ladder: trial steps taken ahead of the accept/reject decisions (1 = off)")
     ap.add_argument("--transport", default="auto", choices=["auto", "peer", "nccl"],
                     help="sharded views: in-kernel all-reduce over NVLink peer memory, or NCCL all-reduces")
     args = ap.parse_args()
@@ -407,6 +409,7 @@ def main():
         prob.set_segment(args.segment)
     if args.loop_mode:
         prob.set_loop_mode(args.loop_mode)
+    prob.set_ladder(args.ladder)
     transport = "none"
     if world > 1:
         from camera_calibration_b200 import sharding
@@ -449,6 +452,7 @@ def main():
         p2 = cc.Problem(model, offs, mp_pin, sp_pin, device=local)
         if world > 1:
             p2.comm_share(prob)
+        p2.set_ladder(args.ladder)
         _, _, it, _ = p2.lm_run(Ploc, MAX_ITERS, want_trace=False)
         p2.close()
         return it
@@ -526,7 +530,7 @@ def main():
             "metric": "lm_iterations_per_sec", "value": value, "unit": "LM iterations/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot_ms / args.steps,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic", "config": dict(workload_config(args, c, offs_all), exchange={
+            "data": "synthetic", "config": dict(workload_config(args, c, offs_all), damping_ladder=args.ladder, exchange={
                 "none": "none (one GPU)",
                 "peer": "reduced system (161 doubles) + trial cost summed inside k_schur / k_cost through NVLink peer memory",
                 "nccl": "two ncclAllReduce per iteration (161 doubles, 1 double)"}[transport]),

@@ -138,6 +138,10 @@ class Problem:
     def set_segment(self, n):
         self._check(self._L.calib_set_segment(self._h, int(n)))
 
+    def set_ladder(self, max_candidates):
+        """damping ladder: trial steps taken ahead of the accept/reject decisions (1 = off, 2, 4)"""
+        self._check(self._L.calib_set_ladder(self._h, int(max_candidates)))
+
     def set_loop_mode(self, mode):
         """0 auto, 1 host-driven iteration graphs, 2 device-driven WHILE graph."""
         self._check(self._L.calib_set_loop_mode(self._h, int(mode)))

@@ -82,6 +82,7 @@ struct calib_handle {
     bool comm_owned = false;
     int nranks = 1, rank = 0;
     std::shared_ptr<PeerComm> peer;        // in-kernel exchange over NVLink peer memory
+    int ladder = kJMax;                    // cap of the damping ladder (1 = one candidate per pass)
     int transport = 0;                     // 0 auto (peer memory when attached, else NCCL), 1 NCCL, 2 peer memory
     double* l2buf = nullptr;
     size_t l2bytes = 0;
@@ -279,7 +280,10 @@ static int build_tasks(calib_handle* h, int seg) {
     Dev& d = h->dev;
     d.ev_warps = ev_warps; d.ev_blocks = (ev_warps + kBlockWarps - 1) / kBlockWarps; d.ev_pieces = (int)evp.size();
     d.co_warps = co_warps; d.co_blocks = (co_warps + kBlockWarps - 1) / kBlockWarps;
-    d.sc_blocks = (int)std::max<int64_t>(1, std::min<int64_t>((M + kBlockWarps - 1) / kBlockWarps, 2 * h->n_sm));
+    // k_schur / k_backsub: one warp per view; the grid repeats the view groups once per candidate
+    // of the damping ladder (blocks of candidates a pass does not have leave at once)
+    d.sc_groups = (int)std::max<int64_t>(1, std::min<int64_t>((M + kBlockWarps - 1) / kBlockWarps, 2 * h->n_sm));
+    d.bs_groups = d.sc_groups;
     Arena a;
     auto records = [](const std::vector<Piece>& pc, const std::vector<int>& ch, const std::vector<int>& ce) {
         std::vector<WarpRec> r(ch.size() - 1);
@@ -296,7 +300,7 @@ static int build_tasks(calib_handle* h, int seg) {
     const size_t meta_bytes = a.bytes;
     const size_t o_pA = a.reserve<double>((size_t)d.ev_blocks * kNA), o_pE = a.reserve<double>(d.ev_blocks);
     const size_t o_pBD = a.reserve<double>((size_t)std::max(d.ev_pieces, 1) * kNBD);
-    const size_t o_pW = a.reserve<double>((size_t)d.sc_blocks * kNBD), o_pC = a.reserve<double>(d.co_blocks);
+    const size_t o_pW = a.reserve<double>((size_t)d.sc_groups * kJMax * kNBD), o_pC = a.reserve<double>((size_t)d.co_blocks * kJMax);
     CUDA_TRY(h, cudaMallocAsync(&h->arena_part, a.bytes, h->stream));
     a.base = (char*)h->arena_part;
     // one upload for the five index tables
@@ -376,9 +380,10 @@ extern "C" int calib_create(calib_t** out, int model, int64_t M, const int64_t* 
         const size_t n = ((size_t)std::max<int64_t>(N, 1) + 31) / 32 * 32;   // array stride: 256-byte aligned
         Arena a;
         const size_t o_soa = a.reserve<double>(5 * n + 64);
-        const size_t o_P = a.reserve<double>((size_t)2 * h->K), o_views = a.reserve<ViewC>((size_t)2 * M);
-        const size_t o_red = a.reserve<double>(kRedN), o_vtab = a.reserve<double>((size_t)M * kVtab);
+        const size_t o_P = a.reserve<double>((size_t)kNBuf * h->K), o_views = a.reserve<ViewC>((size_t)kNBuf * M);
+        const size_t o_red = a.reserve<double>(kRedN), o_vtab = a.reserve<double>((size_t)kJMax * M * kVtab);
         const size_t o_et = a.reserve<double>(8), o_delta = a.reserve<double>((size_t)h->K);
+        const size_t o_dcs = a.reserve<double>(kJMax * 16);
         const size_t o_st = a.reserve<LmState>(1);
         constexpr int kTraceIters = 256;
         const size_t o_trace = a.reserve<double>(4 * kTraceIters);
@@ -390,6 +395,7 @@ extern "C" int calib_create(calib_t** out, int model, int64_t M, const int64_t* 
         d.X = soa; d.Y = soa + n; d.Z = soa + 2 * n; d.U = soa + 3 * n; d.V = soa + 4 * n;
         d.Pbuf = a.at<double>(o_P); d.views = a.at<ViewC>(o_views); d.red = a.at<double>(o_red);
         d.vtab = a.at<double>(o_vtab); d.etrial = a.at<double>(o_et); d.delta = a.at<double>(o_delta);
+        d.dcs = a.at<double>(o_dcs);
         d.st = a.at<LmState>(o_st);
         d.trace = a.at<double>(o_trace);
         h->trace_cap = kTraceIters;
@@ -442,6 +448,14 @@ extern "C" int calib_set_loop_mode(calib_t* h, int mode) {
     if (!h) return fail(nullptr, CALIB_E_ARG, "NULL handle");
     if (mode < 0 || mode > 2) return fail(h, CALIB_E_ARG, "calib_set_loop_mode: 0 auto, 1 host, 2 device");
     h->loop_mode = mode;
+    return CALIB_OK;
+}
+
+extern "C" int calib_set_ladder(calib_t* h, int max_candidates) {
+    if (!h) return fail(nullptr, CALIB_E_ARG, "NULL handle");
+    if (max_candidates != 1 && max_candidates != 2 && max_candidates != kJMax)
+        return fail(h, CALIB_E_ARG, "calib_set_ladder: 1, 2 or 4 candidates");
+    h->ladder = max_candidates;
     return CALIB_OK;
 }
 
@@ -499,7 +513,7 @@ void enqueue_schur(calib_handle* h, Launcher& ln, int fuse_solve) {
     const Dev& d = h->dev;
     cudaEvent_t a, b;
     ln.begin(&a, &b);
-    k_schur<MODEL><<<d.sc_blocks, kBlockThreads, 0, h->stream>>>(d, fuse_solve);
+    k_schur<MODEL><<<d.sc_groups * kJMax, kBlockThreads, 0, h->stream>>>(d, fuse_solve);
     ln.end(KSCHUR, a, b);
     ln.count += 1;
 }
@@ -508,7 +522,7 @@ template <int MODEL>
 void enqueue_solve(calib_handle* h, Launcher& ln) {
     cudaEvent_t a, b;
     ln.begin(&a, &b);
-    k_solve<MODEL><<<1, 32, 0, h->stream>>>(h->dev);
+    k_solve<MODEL><<<1, 32 * kJMax, 0, h->stream>>>(h->dev);
     ln.end(KSOLVE, a, b);
     ln.count += 1;
 }
@@ -518,7 +532,7 @@ void enqueue_backsub(calib_handle* h, Launcher& ln) {
     const Dev& d = h->dev;
     cudaEvent_t a, b;
     ln.begin(&a, &b);
-    k_backsub<MODEL><<<d.sc_blocks, kBlockThreads, 0, h->stream>>>(d);
+    k_backsub<MODEL><<<d.bs_groups * kJMax, kBlockThreads, 0, h->stream>>>(d);
     ln.end(KBACK, a, b);
     ln.count += 1;
 }
@@ -563,7 +577,7 @@ int enqueue_iteration(calib_handle* h, Launcher& ln) {
     enqueue_backsub<MODEL>(h, ln);
     enqueue_cost<MODEL>(h, ln, nccl ? 0 : 1);
     if (nccl) {
-        if (g_nccl.AllReduce(d.etrial, d.etrial, 1, ncclDouble, ncclSum, h->comm, h->stream) != ncclSuccess)
+        if (g_nccl.AllReduce(d.etrial, d.etrial, kJMax, ncclDouble, ncclSum, h->comm, h->stream) != ncclSuccess)
             return fail(h, CALIB_E_COMM, "ncclAllReduce(trial cost) failed");
         if (d.use_cond) k_accept<true><<<1, 1, 0, h->stream>>>(d);
         else k_accept<false><<<1, 1, 0, h->stream>>>(d);
@@ -650,11 +664,12 @@ int upload_to(calib_handle* h, const double* P, int buf) {
     return CALIB_OK;
 }
 
-int push_state(calib_handle* h, double lam, double lam_min, double lam_max, double err_min, int max_iters) {
+int push_state(calib_handle* h, double lam, double lam_min, double lam_max, double err_min, int max_iters, int jmax = 1) {
     LmState s;
     memset(&s, 0, sizeof s);
     s.lam = lam; s.lam_min = lam_min; s.lam_max = lam_max; s.err_min = err_min;
     s.max_iters = max_iters; s.need_eval = 1; s.cur = h->cur; s.nranks = h->nranks;
+    s.J = 1; s.jmax = std::max(1, std::min(jmax, (int)kJMax));
     *h->h_state = s;
     CUDA_TRY(h, cudaMemcpyAsync(h->dev.st, h->h_state, sizeof(LmState), cudaMemcpyHostToDevice, h->stream));
     return CALIB_OK;
@@ -726,7 +741,7 @@ extern "C" int calib_lm_run_resident(calib_t* h, int maxIters, double lam0, doub
     for (auto& pe : h->prof_events) { cudaEventDestroy(pe.second.first); cudaEventDestroy(pe.second.second); }
     h->prof_events.clear();
     for (int i = 0; i < 5; ++i) { h->ktime[i] = 0; h->kcount[i] = 0; }
-    RC(push_state(h, lam0, lam_min, lam_max, err_min, maxIters));
+    RC(push_state(h, lam0, lam_min, lam_max, err_min, maxIters, h->ladder));
     CUDA_TRY(h, cudaEventRecord(h->ev0, h->stream));
     RC(make_views(h, 1));
     Launcher ln{h, prof};
@@ -738,7 +753,7 @@ extern "C" int calib_lm_run_resident(calib_t* h, int maxIters, double lam0, doub
         CUDA_TRY(h, cudaEventRecord(h->ev1, h->stream));
         RC(sync(h));
         // skipped evaluations (after a rejected step) still launch and return at once
-        ln.count += (int64_t)kpi * h->h_state->iter;
+        ln.count += (int64_t)kpi * h->h_state->n_pass;
     } else {
         int enq = 0;
         int batch = 2;   // iterations enqueued between two looks at the device state

@@ -22,8 +22,24 @@ constexpr int kBlockThreads = 256;          // every kernel of this path: 8 warp
 constexpr int kBlockWarps = kBlockThreads / 32;
 constexpr int kNA = 64;                     // padded slot count of the intrinsic sweep
 constexpr int kNBD = 96;                    // padded slot count of a piece row and of W
-constexpr int kRedA = 0, kRedW = kNA, kRedE = kNA + kNBD, kRedN = kNA + kNBD + 1;
 constexpr int kVtab = 88;                   // per view: Cholesky factor (21) + Z (6 (L+1)), padded
+
+// Damping ladder.  After a rejected step the reference only multiplies lambda by 10 and tries again
+// from the same point with the same normal equations (src/calibrate.py:161-166), so the next few
+// trial steps can be taken AHEAD of the decisions: one pass of k_schur / k_backsub / k_cost handles
+// J candidates lambda, 10 lambda, ... (J = 1 after an accepted step, doubling after rejected ones up
+// to kJMax); the accept step then replays the reference's decisions one candidate at a time and
+// drops the candidates after the first accepted one.  Iterates, costs, lambdas, trace rows and the
+// iteration count are those of the one-at-a-time loop (the sums of candidate j do not depend on J);
+// the latency-bound tail of the iteration and the sweep over the detections are paid once per J.
+constexpr int kJMax = 4;
+constexpr int kNBuf = kJMax + 1;            // parameter / view-constant buffers: current + kJMax trial
+// red[]: A slots (and g_c), the cost, then W (and w) of every candidate
+constexpr int kRedA = 0, kRedE = kNA, kRedW0 = kNA + 8;
+__host__ __device__ constexpr int red_w(int j) { return kRedW0 + kNBD * j; }
+__host__ __device__ constexpr int red_n(int J) { return kRedW0 + kNBD * J; }
+constexpr int kRedN = red_n(kJMax);         // 456
+__host__ __device__ inline int trial_buf(int cur, int j) { const int s = cur + 1 + j; return s >= kNBuf ? s - kNBuf : s; }
 
 // <= count points of ONE view, contiguous in the point arrays
 struct Piece { int view, start, count, pad; };
@@ -34,7 +50,9 @@ struct LmState {
     double lam, E_cur, E_trial, sse;
     double lam_min, lam_max, err_min;
     int iter, max_iters, done, need_eval, cur, nranks;
-    int comm_fail, pad0;   // comm_fail: a peer never arrived at an exchange (calib_peer.cuh)
+    int comm_fail;         // a peer never arrived at an exchange (calib_peer.cuh)
+    int J, jmax;           // candidates of this pass of the damping ladder; its cap (1 = ladder off)
+    int n_pass;            // passes (one k_schur/k_backsub/k_cost each) so far
     unsigned int cnt_schur, cnt_cost;
     long long n_eval;   // Jacobian evaluations actually executed
 };
@@ -44,24 +62,26 @@ struct Dev {  // everything the kernels need; passed by value
     long long N, K;
     int ev_warps, ev_blocks, ev_pieces;   // partition of the points for k_eval
     int co_warps, co_blocks;              // partition for k_cost
-    int sc_blocks;                        // view blocks of k_schur (one more block sums A)
+    int sc_groups;                        // k_schur: view groups (grid = sc_groups x kJMax)
+    int bs_groups;                        // k_backsub: view groups (grid = bs_groups x kJMax)
     const double *X, *Y, *Z, *U, *V;      // SoA detections
     const Piece* ev_piece;                // ev_pieces, in point (= view) order
     const WarpRec* ev_rec;                // ev_warps    : piece range (and first piece) of warp w
     const int* view_piece;                // M + 1       : piece range of view v
     const Piece* co_piece;
     const WarpRec* co_rec;                // co_warps
-    double* Pbuf;                         // 2 x K
-    ViewC* views;                         // 2 x M
+    double* Pbuf;                         // kNBuf x K
+    ViewC* views;                         // kNBuf x M
     double* partA;                        // ev_blocks x kNA
     double* partE;                        // ev_blocks
     double* partBD;                       // ev_pieces x kNBD
-    double* partW;                        // sc_blocks x kNBD
+    double* partW;                        // kJMax x sc_groups x kNBD
     double* red;                          // kRedN : the reduced system, all-reduced when sharded
-    double* vtab;                         // M x kVtab
-    double* partC;                        // co_blocks (trial cost)
-    double* etrial;                       // 1
+    double* vtab;                         // kJMax x M x kVtab
+    double* partC;                        // co_blocks x kJMax (trial costs)
+    double* etrial;                       // kJMax
     double* delta;                        // K
+    double* dcs;                          // kJMax x 16: step of the shared parameters, per candidate
     double* trace;                        // max_iters x 4
     LmState* st;
     cudaGraphConditionalHandle cond;      // WHILE node of the whole-loop graph
@@ -157,25 +177,35 @@ __device__ __forceinline__ void accum_BD(const PointOut<MODEL>& o, double (&acc)
 // boundaries, so a load is never waited for inside the FP64 stream.  `begin(piece, index)` runs
 // after the view constants are in sview (warp-synchronised), `body(point)` per point of the
 // lane, `end(piece, index)` with all 32 lanes converged.
-template <class Begin, class Body, class End>
+template <int NV, class Begin, class Body, class End>
 __device__ __forceinline__ void sweep_pieces(const Dev& d, const Piece* __restrict__ pieces, const WarpRec& rec,
-                                             const ViewC* __restrict__ views, ViewC& sview, int lane,
+                                             const ViewC* const (&views)[NV], ViewC (&sview)[NV], int lane,
                                              Begin begin, Body body, End end) {
     const int p0 = rec.p0, p1 = rec.p1;
     if (p0 >= p1) return;
     Piece cur = rec.first;
     Pt pn;
     if (lane < cur.count) load_point(d, (long long)cur.start + lane, pn);
-    double vn = 0.0;
-    if (lane < kViewDoubles) vn = reinterpret_cast<const double*>(views + cur.view)[lane];
+    double vn[NV];
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+        vn[j] = 0.0;
+        if (lane < kViewDoubles) vn[j] = reinterpret_cast<const double*>(views[j] + cur.view)[lane];
+    }
     for (int pi = p0; pi < p1; ++pi) {
         const bool has_next = pi + 1 < p1;
         Piece nxt = cur;
         if (has_next) nxt = pieces[pi + 1];
         __syncwarp();
-        if (lane < kViewDoubles) reinterpret_cast<double*>(&sview)[lane] = vn;
+        if (lane < kViewDoubles) {
+#pragma unroll
+            for (int j = 0; j < NV; ++j) reinterpret_cast<double*>(&sview[j])[lane] = vn[j];
+        }
         __syncwarp();
-        if (has_next && lane < kViewDoubles) vn = reinterpret_cast<const double*>(views + nxt.view)[lane];
+        if (has_next && lane < kViewDoubles) {
+#pragma unroll
+            for (int j = 0; j < NV; ++j) vn[j] = reinterpret_cast<const double*>(views[j] + nxt.view)[lane];
+        }
         begin(cur, pi);
         if (lane >= cur.count && has_next && lane < nxt.count) load_point(d, (long long)nxt.start + lane, pn);
         for (int i = lane; i < cur.count; i += 32) {
@@ -194,7 +224,7 @@ __device__ __forceinline__ void sweep_pieces(const Dev& d, const Piece* __restri
 __global__ void k_make_views(Dev d, int which_is_cur) {
     const int v = blockIdx.x * blockDim.x + threadIdx.x;
     if (v >= d.M) return;
-    const int b = which_is_cur ? d.st->cur : (d.st->cur ^ 1);
+    const int b = which_is_cur ? d.st->cur : trial_buf(d.st->cur, 0);
     ViewC w;
     make_view(d.Pbuf + (long long)b * d.K + d.L + 6ll * v, w);
     d.views[(long long)b * d.M + v] = w;

@@ -17,15 +17,15 @@ constexpr size_t kCostDynSmem = kBlockWarps * sizeof(CostRing);
 
 extern __shared__ __align__(128) unsigned char dyn_smem[];
 
-template <bool TMA, int D, int WS, class Begin, class Body, class End>
+template <bool TMA, int D, int WS, int NV, class Begin, class Body, class End>
 __device__ __forceinline__ void sweep(const Dev& d, const Piece* __restrict__ pieces, const WarpRec& rec,
-                                      const ViewC* __restrict__ views, ViewC& sview, int warp, unsigned long long* bars,
-                                      int lane, Begin begin, Body body, End end) {
+                                      const ViewC* const (&views)[NV], ViewC (&sview)[NV], int warp,
+                                      unsigned long long* bars, int lane, Begin begin, Body body, End end) {
     if constexpr (TMA) {
         PointRing<D, WS>* ring = reinterpret_cast<PointRing<D, WS>*>(dyn_smem);
-        sweep_windows<D, WS>(d, pieces, rec, views, sview, ring[warp], bars, lane, begin, body, end);
+        sweep_windows<D, WS, NV>(d, pieces, rec, views, sview, ring[warp], bars, lane, begin, body, end);
     } else {
-        sweep_pieces(d, pieces, rec, views, sview, lane, begin, body, end);
+        sweep_pieces<NV>(d, pieces, rec, views, sview, lane, begin, body, end);
     }
 }
 
@@ -42,12 +42,12 @@ __global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
     const LmState* st = d.st;
     if (st->done || !st->need_eval) return;
     __shared__ double sc[16];
-    __shared__ __align__(16) ViewC sview[kBlockWarps];
+    __shared__ __align__(16) ViewC sview[kBlockWarps][1];
     __shared__ double sred[kBlockWarps][kNA];
     __shared__ double sE[kBlockWarps];
     const int cur = st->cur;
     const double* P = d.Pbuf + (long long)cur * d.K;
-    const ViewC* views = d.views + (long long)cur * d.M;
+    const ViewC* const views[1] = {d.views + (long long)cur * d.M};
     if (threadIdx.x < L) sc[threadIdx.x] = P[threadIdx.x];
     __syncthreads();
     // sweep 1: B_v, D_v, g_v -- one row of kNBD slots per piece
@@ -55,11 +55,11 @@ __global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
         double acc[kNBD];
 #pragma unroll
         for (int i = 0; i < kNBD; ++i) acc[i] = 0.0;
-        sweep<false, 1, 1>(d, d.ev_piece, rec, views, sview[warp], warp, nullptr, lane,
+        sweep<false, 1, 1, 1>(d, d.ev_piece, rec, views, sview[warp], warp, nullptr, lane,
             [&](const Piece&, int) {},
             [&](const Pt& p) {
                 PointOut<MODEL> o;
-                point_eval<MODEL, true, true>(sc, sview[warp], p.X, p.Y, p.Z, p.U, p.V, o);
+                point_eval<MODEL, true, true>(sc, sview[warp][0], p.X, p.Y, p.Z, p.U, p.V, o);
                 accum_BD<MODEL>(o, acc);
             },
             [&](const Piece&, int pi) {
@@ -77,11 +77,11 @@ __global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
 #pragma unroll
         for (int i = 0; i < kNA; ++i) acc[i] = 0.0;
         double e = 0.0;
-        sweep<false, 1, 1>(d, d.ev_piece, rec, views, sview[warp], warp, nullptr, lane,
+        sweep<false, 1, 1, 1>(d, d.ev_piece, rec, views, sview[warp], warp, nullptr, lane,
             [&](const Piece&, int) {},
             [&](const Pt& p) {
                 PointOut<MODEL> o;
-                point_eval<MODEL, true, false>(sc, sview[warp], p.X, p.Y, p.Z, p.U, p.V, o);
+                point_eval<MODEL, true, false>(sc, sview[warp][0], p.X, p.Y, p.Z, p.U, p.V, o);
                 accum_A<MODEL>(o, acc, e);
             },
             [&](const Piece&, int) {});
@@ -106,24 +106,39 @@ __global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
 }
 
 // ---- accept / reject, lambda update, termination: src/calibrate.py:155-168 ------------------
+// Replays the reference's decisions over the J candidates of this pass (calib_kernels.cuh, "damping
+// ladder"): candidate j is the reference's iteration iter+j with damping lam * 10^j; the first
+// accepted one ends the pass, the rest is dropped.
 // COND: the launch sits inside the WHILE node of the whole-loop graph and sets its condition.  (Kept
 // out of the plain variants: a kernel that calls the device runtime cannot be profiled by ncu.)
 template <bool COND>
 __device__ __forceinline__ void lm_accept(const Dev& d) {
     LmState* st = d.st;
-    const double E = st->E_cur, E1 = d.etrial[0], lam = st->lam;
-    const int it = st->iter;
-    const bool acc = E1 < E;   // strict; NaN rejects
-    double* tr = d.trace + 4ll * it;
-    tr[0] = E; tr[1] = E1; tr[2] = lam; tr[3] = acc ? 1.0 : 0.0;
-    double nl;
-    if (acc) { st->cur ^= 1; nl = lam / 10.0; st->need_eval = 1; st->E_cur = E1; }
-    else     { nl = lam * 10.0; st->need_eval = 0; }
-    st->lam = nl;
-    st->E_trial = E1;
+    const int J = st->J, cur = st->cur;
+    double lam = st->lam;
+    const double E = st->E_cur;
+    int it = st->iter, done = 0;
+    bool accepted = false;
+    for (int j = 0; j < J && !done && !accepted; ++j) {
+        const double E1 = d.etrial[j];
+        const bool acc = E1 < E;   // strict; NaN rejects
+        double* tr = d.trace + 4ll * it;
+        tr[0] = E; tr[1] = E1; tr[2] = lam; tr[3] = acc ? 1.0 : 0.0;
+        if (acc) { st->cur = trial_buf(cur, j); lam = lam / 10.0; st->E_cur = E1; accepted = true; }
+        else     { lam = lam * 10.0; }
+        st->E_trial = E1;
+        it += 1;
+        done = (!(st->lam_min < lam && lam < st->lam_max) || E < st->err_min || it >= st->max_iters) ? 1 : 0;
+    }
+    st->need_eval = accepted ? 1 : 0;
+    st->lam = lam;
     st->sse = E;
-    st->iter = it + 1;
-    const int done = (!(st->lam_min < nl && nl < st->lam_max) || E < st->err_min || it + 1 >= st->max_iters) ? 1 : 0;
+    st->iter = it;
+    st->n_pass += 1;
+    int nj = accepted ? 1 : 2 * J;
+    if (nj > st->jmax) nj = st->jmax;
+    if (nj > st->max_iters - it) nj = st->max_iters - it;
+    st->J = nj < 1 ? 1 : nj;
     if (done) st->done = 1;
     if (COND) cudaGraphSetConditional(d.cond, done ? 0u : 1u);
 }
@@ -134,7 +149,29 @@ __global__ void k_accept(Dev d) {
     lm_accept<COND>(d);
 }
 
-// ---- cost-only sweep at the trial point -------------------------------------------------------
+// ---- cost-only sweep at the J trial points ------------------------------------------------------
+template <int MODEL, bool TMA, int NJ>
+__device__ __forceinline__ void cost_sweep(const Dev& d, const WarpRec& rec, int cur, double (*sc)[16],
+                                           ViewC (&sview)[kJMax], unsigned long long* bars, int warp, int lane,
+                                           double (&e)[kJMax]) {
+    const ViewC* views[NJ];
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) views[j] = d.views + (long long)trial_buf(cur, j) * d.M;
+    const ViewC* const (&cviews)[NJ] = views;
+    ViewC (&sv)[NJ] = reinterpret_cast<ViewC (&)[NJ]>(sview);
+    sweep<TMA, kCostStages, kWinSteps, NJ>(d, d.co_piece, rec, cviews, sv, warp, bars, lane,
+        [&](const Piece&, int) {},
+        [&](const Pt& p) {
+#pragma unroll
+            for (int j = 0; j < NJ; ++j) {
+                PointOut<MODEL> o;
+                point_eval<MODEL, false, false>(sc[j], sv[j], p.X, p.Y, p.Z, p.U, p.V, o);
+                e[j] = __dadd_rn(e[j], fma(o.rv, o.rv, __dmul_rn(o.ru, o.ru)));
+            }
+        },
+        [&](const Piece&, int) {});
+}
+
 template <int MODEL, bool COND, bool TMA>
 __global__ void __launch_bounds__(kBlockThreads, 2) k_cost(Dev d, int fuse_accept) {
     constexpr int L = ModelTraits<MODEL>::L;
@@ -148,50 +185,56 @@ __global__ void __launch_bounds__(kBlockThreads, 2) k_cost(Dev d, int fuse_accep
         if (COND) { if (blockIdx.x == 0 && threadIdx.x == 0) cudaGraphSetConditional(d.cond, 0u); }
         return;
     }
-    __shared__ double sc[16];
-    __shared__ __align__(16) ViewC sview[kBlockWarps];
-    __shared__ double sE[kBlockWarps];
-    __shared__ double s_tot;
+    __shared__ double sc[kJMax][16];
+    __shared__ __align__(16) ViewC sview[kBlockWarps][kJMax];
+    __shared__ double sE[kBlockWarps][kJMax];
+    __shared__ double s_tot[kJMax];
     __shared__ int s_last;
     __shared__ __align__(8) unsigned long long bars[kBlockWarps][kCostStages];
-    const int tb = st->cur ^ 1;
-    const double* P = d.Pbuf + (long long)tb * d.K;
-    const ViewC* views = d.views + (long long)tb * d.M;
-    if (threadIdx.x < L) sc[threadIdx.x] = P[threadIdx.x];
+    const int cur = st->cur, J = st->J;
+    if (threadIdx.x < kJMax * 16) {
+        const int j = threadIdx.x >> 4, i = threadIdx.x & 15;
+        if (j < J && i < L) sc[j][i] = d.Pbuf[(long long)trial_buf(cur, j) * d.K + i];
+    }
     __syncthreads();
-    double e = 0.0;
-    sweep<TMA, kCostStages, kWinSteps>(d, d.co_piece, rec, views, sview[warp], warp, bars[warp], lane,
-        [&](const Piece&, int) {},
-        [&](const Pt& p) {
-            PointOut<MODEL> o;
-            point_eval<MODEL, false, false>(sc, sview[warp], p.X, p.Y, p.Z, p.U, p.V, o);
-            e = __dadd_rn(e, fma(o.rv, o.rv, __dmul_rn(o.ru, o.ru)));
-        },
-        [&](const Piece&, int) {});
-    e = warp_sum(e);
-    if (lane == 0) sE[warp] = e;
+    double e[kJMax];
+#pragma unroll
+    for (int j = 0; j < kJMax; ++j) e[j] = 0.0;
+    if (J == 1) cost_sweep<MODEL, TMA, 1>(d, rec, cur, sc, sview[warp], bars[warp], warp, lane, e);
+    else if (J == 2) cost_sweep<MODEL, TMA, 2>(d, rec, cur, sc, sview[warp], bars[warp], warp, lane, e);
+    else cost_sweep<MODEL, TMA, kJMax>(d, rec, cur, sc, sview[warp], bars[warp], warp, lane, e);
+#pragma unroll
+    for (int j = 0; j < kJMax; ++j) {
+        const double s = warp_sum(e[j]);
+        if (lane == 0) sE[warp][j] = s;
+    }
+    __syncthreads();
+    if (threadIdx.x < kJMax) {
+        double s = sE[0][threadIdx.x];
+#pragma unroll
+        for (int k = 1; k < kBlockWarps; ++k) s = __dadd_rn(s, sE[k][threadIdx.x]);
+        d.partC[(long long)blockIdx.x * kJMax + threadIdx.x] = s;
+        __threadfence();
+    }
     __syncthreads();
     if (threadIdx.x == 0) {
-        double s = sE[0];
-#pragma unroll
-        for (int k = 1; k < kBlockWarps; ++k) s = __dadd_rn(s, sE[k]);
-        d.partC[blockIdx.x] = s;
-        __threadfence();
         const unsigned int prev = atomicAdd(&st->cnt_cost, 1u);
         s_last = (prev == gridDim.x - 1);
     }
     __syncthreads();
     if (!s_last) return;
     __threadfence();
-    if (warp == 0) {
-        const double tot = warp_sum_array(d.partC, d.co_blocks, lane);
-        if (lane == 0) s_tot = tot;
+    if (warp < kJMax) {     // warp j sums column j, fixed order
+        double acc = 0.0;
+        for (int i = lane; i < d.co_blocks; i += 32) acc = __dadd_rn(acc, __ldcg(d.partC + (long long)i * kJMax + warp));
+        acc = warp_sum(acc);
+        if (lane == 0) s_tot[warp] = acc;
     }
     __syncthreads();
     bool ok = true;
-    if (d.peer.nranks > 1) ok = peer_allreduce(d.peer, 1, &s_tot, 1, &s_last);   // views sharded: sum over the ranks
+    if (d.peer.nranks > 1) ok = peer_allreduce(d.peer, 1, s_tot, J, &s_last);   // views sharded: sum over the ranks
     if (threadIdx.x == 0) {
-        d.etrial[0] = s_tot;
+        for (int j = 0; j < kJMax; ++j) d.etrial[j] = s_tot[j];
         st->cnt_cost = 0;
         if (!ok) {
             st->comm_fail = 1; st->done = 1;

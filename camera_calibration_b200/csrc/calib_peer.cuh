@@ -1,8 +1,8 @@
 // All-reduce of the reduced system over NVLink peer memory, inside the kernels that produce it.
 //
 // When the views of one calibration are sharded over the GPUs of a node the
-// only exchange per LM iteration is the reduced system (kRedN = 161 doubles) and the scalar trial
-// cost.  A library collective costs a launch (plus a 1-thread kernel to consume it) per exchange and
+// only exchange per LM iteration is the reduced system (72 + 96 doubles per candidate of the damping
+// ladder) and the trial costs.  A library collective costs a launch (plus a 1-thread kernel to consume it) per exchange and
 // keeps the WHILE-graph loop off the table; here the last thread block of k_schur / k_cost does it:
 //   push   thread t stores value t of its rank's contribution into a slot of EVERY peer's inbox,
 //          through the NVLink mapping of the peer's memory, as ONE 16-byte store
@@ -22,7 +22,7 @@
 namespace calib {
 
 constexpr int kPeerMaxRanks = 8;
-constexpr int kPeerSlot = 168;            // elements per slot (>= the 161 of the reduced system)
+constexpr int kPeerSlot = 464;            // elements per slot (>= kRedN, the reduced systems of a full damping ladder)
 constexpr int kPeerChannels = 2;
 constexpr size_t kPeerInboxElems = (size_t)kPeerChannels * 2 * kPeerMaxRanks * kPeerSlot;   // uint4 each
 constexpr size_t kPeerInboxBytes = kPeerInboxElems * 16;
@@ -54,7 +54,7 @@ __device__ __forceinline__ size_t peer_slot_off(int ch, int par, int src) {
     return ((size_t)(ch * 2 + par) * kPeerMaxRanks + src) * kPeerSlot;
 }
 
-// Called by ALL threads of one block (blockDim.x >= n).  val[0..n) in shared memory is this rank's
+// Called by ALL threads of one block.  val[0..n) in shared memory is this rank's
 // contribution and is replaced by the sum over ranks.  Returns false on timeout.
 __device__ __forceinline__ bool peer_allreduce(const PeerDev& pc, int ch, double* val, int n, int* s_flag) {
     const int tid = threadIdx.x;
@@ -63,18 +63,21 @@ __device__ __forceinline__ bool peer_allreduce(const PeerDev& pc, int ch, double
     const int par = (int)(seq & 1u);
     if (tid == 0) *s_flag = 1;
     __syncthreads();
-    if (tid < n) {
-        const double mine = val[tid];
+    for (int e = tid; e < n; e += (int)blockDim.x) {
+        const double mine = val[e];
         const unsigned long long bits = (unsigned long long)__double_as_longlong(mine);
         const uint4 pk = make_uint4((unsigned)bits, seq, (unsigned)(bits >> 32), seq);
-        const size_t off = peer_slot_off(ch, par, pc.rank) + tid;
+        const size_t off = peer_slot_off(ch, par, pc.rank) + e;
         for (int p = 0; p < pc.nranks; ++p)
             if (p != pc.rank) st_volatile_v4(pc.box[p] + off, pk);
+    }
+    for (int e = tid; e < n; e += (int)blockDim.x) {
+        const double mine = val[e];
         double s = 0.0;
         for (int r = 0; r < pc.nranks; ++r) {
             double v = mine;
             if (r != pc.rank) {
-                const uint4* src = pc.box[pc.rank] + peer_slot_off(ch, par, r) + tid;
+                const uint4* src = pc.box[pc.rank] + peer_slot_off(ch, par, r) + e;
                 uint4 g = ld_volatile_v4(src);
                 if (g.y != seq || g.w != seq) {
                     const unsigned long long t0 = global_timer_ns();
@@ -88,7 +91,7 @@ __device__ __forceinline__ bool peer_allreduce(const PeerDev& pc, int ch, double
             }
             s = __dadd_rn(s, v);
         }
-        val[tid] = s;
+        val[e] = s;
     }
     __syncthreads();
     if (tid == 0) pc.seq[ch] = seq;

@@ -100,21 +100,28 @@ __device__ __forceinline__ double solve_reduced_core(const double* redA, const d
 // E: the cost at the current point as the evaluation pass summed it.  It seeds the loop; from the
 // second iteration on the current cost IS the trial cost of the last accepted step (set by
 // lm_accept), as in the reference where both numbers come from one function (calibrate.py:155-156).
+// j: candidate of the damping ladder (lam * 10^j, trial buffer j).
 template <int MODEL, class Ld>
 __device__ __forceinline__ void solve_reduced(const Dev& d, const double* redA, const double* redW, double E,
-                                              int lane, Ld ld) {
+                                              int j, int lane, Ld ld) {
     constexpr int L = ModelTraits<MODEL>::L;
     LmState* st = d.st;
-    const double dc = solve_reduced_core<MODEL>(redA, redW, st->lam, lane, ld);
+    double lam = st->lam;
+    for (int k = 0; k < j; ++k) lam = lam * 10.0;      // the reference's own update chain
+    const double dc = solve_reduced_core<MODEL>(redA, redW, lam, lane, ld);
     const int cur = st->cur;
     if (lane < L) {
-        d.delta[lane] = dc;
-        d.Pbuf[(long long)(cur ^ 1) * d.K + lane] = d.Pbuf[(long long)cur * d.K + lane] + dc;
+        if (j == 0) d.delta[lane] = dc;
+        d.dcs[j * 16 + lane] = dc;
+        d.Pbuf[(long long)trial_buf(cur, j) * d.K + lane] = d.Pbuf[(long long)cur * d.K + lane] + dc;
     }
-    if (lane == 0 && st->iter == 0) st->E_cur = E;
+    if (j == 0 && lane == 0 && st->iter == 0) st->E_cur = E;
 }
 
 // ---- per-view Schur stage -------------------------------------------------------------------------
+// Grid = sc_groups x kJMax blocks: block (g, j) works for candidate j of the damping ladder (and
+// leaves at once when the pass has fewer candidates) on views 8 g + warp + k * 8 sc_groups, so the
+// views and the summation order of a candidate do not depend on how many candidates the pass has.
 template <int MODEL>
 __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) {
     using T = ModelTraits<MODEL>;
@@ -126,11 +133,13 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
     __shared__ double sz[kBlockWarps][NZ * 6];     // Z = L^-1 [B^T | g_v], column-major by c
     __shared__ double sl[kBlockWarps][24];         // packed lower factor of the view block
     __shared__ double sga[kBlockWarps][kNA], sge[kBlockWarps];
-    __shared__ double sred[kPeerSlot];             // the reduced system in the layout of red[]
+    __shared__ double sred[kRedN];                 // the reduced system in the layout of red[]
     __shared__ int s_last;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int nvb = d.sc_blocks;
-    {
+    const int nvb = d.sc_groups;
+    const int J = st->J;
+    const int cand = blockIdx.x / nvb, grp = blockIdx.x - cand * nvb;
+    if (cand < J) {
         // which entries of W this lane accumulates: e = lane + 32 k  ->  (p, c), c in [p, L]
         int ep[3], ec[3];
 #pragma unroll
@@ -146,8 +155,10 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
             }
         }
         double wacc[3] = {0.0, 0.0, 0.0};
-        const double lam = st->lam;
-        for (int v = blockIdx.x * kBlockWarps + warp; v < d.M; v += nvb * kBlockWarps) {
+        double lam = st->lam;
+        for (int k = 0; k < cand; ++k) lam = lam * 10.0;
+        double* vtab = d.vtab + (long long)cand * d.M * kVtab;
+        for (int v = grp * kBlockWarps + warp; v < d.M; v += nvb * kBlockWarps) {
             const int r0 = d.view_piece[v], r1 = d.view_piece[v + 1];
             double s0 = 0.0, s1 = 0.0, s2 = 0.0;
             for (int r = r0; r < r1; ++r) {
@@ -168,7 +179,7 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
                 }
             double id[6];
             chol_inplace<6>(Lc, id);
-            double* vt = d.vtab + (long long)v * kVtab;
+            double* vt = vtab + (long long)v * kVtab;
             if (lane == 0) {
 #pragma unroll
                 for (int a = 0; a < 6; ++a)
@@ -210,13 +221,13 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
             double s = sv[0][tid];
 #pragma unroll
             for (int k = 1; k < kBlockWarps; ++k) s += sv[k][tid];
-            d.partW[(long long)blockIdx.x * kNBD + tid] = s;
+            d.partW[((long long)cand * nvb + grp) * kNBD + tid] = s;
         }
     }
     // The last block to finish gathers, in one round trip and in a fixed order, the block rows of W,
     // the block rows of the intrinsic sweep (A, g_c) and the block costs; it publishes the reduced
-    // system (red[], all-reduced when the views are sharded) and, on one GPU, solves it from
-    // shared memory straight away.
+    // system (summed over the ranks when the views are sharded) and solves it from shared memory,
+    // one warp per candidate.
     __threadfence();
     __syncthreads();
     if (tid == 0) {
@@ -227,12 +238,7 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
     if (!s_last) return;
     __threadfence();
     {
-        double s0 = 0.0, s1 = 0.0, s2 = 0.0, a0 = 0.0, a1 = 0.0, e = 0.0;
-#pragma unroll 4
-        for (int r = warp; r < nvb; r += kBlockWarps) {
-            const double* row = d.partW + (long long)r * kNBD;
-            s0 += __ldcg(row + lane); s1 += __ldcg(row + lane + 32); s2 += __ldcg(row + lane + 64);
-        }
+        double a0 = 0.0, a1 = 0.0, e = 0.0;
 #pragma unroll 4
         for (int r = warp; r < d.ev_blocks; r += kBlockWarps) {
             const double* row = d.partA + (long long)r * kNA;
@@ -240,49 +246,64 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
         }
         for (int r = tid; r < d.ev_blocks; r += kBlockThreads) e = __dadd_rn(e, __ldcg(d.partE + r));
         e = warp_sum(e);
-        sv[warp][lane] = s0; sv[warp][lane + 32] = s1; sv[warp][lane + 64] = s2;
         sga[warp][lane] = a0; sga[warp][lane + 32] = a1;
         if (lane == 0) sge[warp] = e;
     }
-    __syncthreads();
-    if (tid < kNBD) {
-        double s = sv[0][tid];
+    for (int j = 0; j < J; ++j) {
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0;
+#pragma unroll 4
+        for (int r = warp; r < nvb; r += kBlockWarps) {
+            const double* row = d.partW + ((long long)j * nvb + r) * kNBD;
+            s0 += __ldcg(row + lane); s1 += __ldcg(row + lane + 32); s2 += __ldcg(row + lane + 64);
+        }
+        __syncthreads();          // sv of the previous candidate has been consumed
+        sv[warp][lane] = s0; sv[warp][lane + 32] = s1; sv[warp][lane + 64] = s2;
+        __syncthreads();
+        if (tid < kNBD) {
+            double s = sv[0][tid];
 #pragma unroll
-        for (int k = 1; k < kBlockWarps; ++k) s += sv[k][tid];
-        sred[kRedW + tid] = s;
-    } else if (tid < kNBD + kNA) {
-        const int c = tid - kNBD;
-        double s = sga[0][c];
+            for (int k = 1; k < kBlockWarps; ++k) s += sv[k][tid];
+            sred[red_w(j) + tid] = s;
+        }
+    }
+    if (tid < kNA) {
+        double s = sga[0][tid];
 #pragma unroll
-        for (int k = 1; k < kBlockWarps; ++k) s += sga[k][c];
-        sred[kRedA + c] = s;
-    } else if (tid == kNBD + kNA) {
+        for (int k = 1; k < kBlockWarps; ++k) s += sga[k][tid];
+        sred[kRedA + tid] = s;
+    } else if (tid == kNA) {
         double s = sge[0];
 #pragma unroll
         for (int k = 1; k < kBlockWarps; ++k) s = __dadd_rn(s, sge[k]);
         sred[kRedE] = s;
         st->cnt_schur = 0;
         if (st->need_eval) st->n_eval += 1;
+    } else if (tid < kRedW0) {
+        sred[tid] = 0.0;
     }
     __syncthreads();
     // views sharded over the GPUs of the node: sum the reduced systems of all ranks, right here
-    if (d.peer.nranks > 1 && !peer_allreduce(d.peer, 0, sred, kRedN, &s_last)) {
+    if (d.peer.nranks > 1 && !peer_allreduce(d.peer, 0, sred, red_n(J), &s_last)) {
         if (tid == 0) { st->comm_fail = 1; st->done = 1; }
         return;
     }
-    if (tid < kRedN) d.red[tid] = sred[tid];
-    if (fuse_solve && warp == 0)
-        solve_reduced<MODEL>(d, sred + kRedA, sred + kRedW, sred[kRedE], lane, LdPlain());
+    for (int e = tid; e < red_n(J); e += kBlockThreads) d.red[e] = sred[e];
+    if (fuse_solve && warp < J)
+        solve_reduced<MODEL>(d, sred + kRedA, sred + red_w(warp), sred[kRedE], warp, lane, LdPlain());
 }
 
-// reduced solve as its own launch (after the all-reduce when the views are sharded)
+// reduced solve as its own launch (after the all-reduce when NCCL sums the reduced systems):
+// one warp per candidate
 template <int MODEL>
 __global__ void k_solve(Dev d) {
     if (d.st->done) return;
-    solve_reduced<MODEL>(d, d.red + kRedA, d.red + kRedW, __ldcg(d.red + kRedE), threadIdx.x, LdCg());
+    const int j = threadIdx.x >> 5;
+    if (j < d.st->J)
+        solve_reduced<MODEL>(d, d.red + kRedA, d.red + red_w(j), __ldcg(d.red + kRedE), j, threadIdx.x & 31, LdCg());
 }
 
-// ---- back-substitution, trial parameters and trial view constants: one warp per view -------------
+// ---- back-substitution, trial parameters and trial view constants: one warp per view; grid =
+// bs_groups x kJMax, block (g, j) works for candidate j ---
 template <int MODEL>
 __global__ void __launch_bounds__(kBlockThreads) k_backsub(Dev d) {
     using T = ModelTraits<MODEL>;
@@ -291,16 +312,23 @@ __global__ void __launch_bounds__(kBlockThreads) k_backsub(Dev d) {
     if (st->done) return;
     __shared__ double srow[kBlockWarps][kVtab];
     __shared__ double sx[kBlockWarps][8];
-    __shared__ double sdc[16];
+    __shared__ double sdc[kJMax][16];
     __shared__ __align__(16) ViewC sview[kBlockWarps];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int cur = st->cur;
+    const int cur = st->cur, J = st->J;
     const double* P = d.Pbuf + (long long)cur * d.K;
-    double* Pt = d.Pbuf + (long long)(cur ^ 1) * d.K;
-    if (tid < L) sdc[tid] = d.delta[tid];
+    if (tid < kJMax * 16) {
+        const int j = tid >> 4, i = tid & 15;
+        if (j < J && i < L) sdc[j][i] = d.dcs[j * 16 + i];
+    }
     __syncthreads();
-    for (int v = blockIdx.x * kBlockWarps + warp; v < d.M; v += gridDim.x * kBlockWarps) {
-        const double* vt = d.vtab + (long long)v * kVtab;
+    const int nb = d.bs_groups;
+    const int j = blockIdx.x / nb, grp = blockIdx.x - j * nb;
+    if (j >= J) return;
+    const int tb = trial_buf(cur, j);
+    for (int v = grp * kBlockWarps + warp; v < d.M; v += nb * kBlockWarps) {
+        double* Pt = d.Pbuf + (long long)tb * d.K;
+        const double* vt = d.vtab + ((long long)j * d.M + v) * kVtab;
         __syncwarp();
         srow[warp][lane] = vt[lane];
         srow[warp][lane + 32] = vt[lane + 32];
@@ -311,7 +339,7 @@ __global__ void __launch_bounds__(kBlockThreads) k_backsub(Dev d) {
         if (lane < 6) {
             double s = Zm[L * 6 + lane];
 #pragma unroll
-            for (int p = 0; p < L; ++p) s = fma(-Zm[p * 6 + lane], sdc[p], s);
+            for (int p = 0; p < L; ++p) s = fma(-Zm[p * 6 + lane], sdc[j][p], s);
             sx[warp][lane] = s;
         }
         __syncwarp();
@@ -332,13 +360,13 @@ __global__ void __launch_bounds__(kBlockThreads) k_backsub(Dev d) {
                 const long long idx = L + 6ll * v + i;
                 e[i] = P[idx] + x[i];
                 Pt[idx] = e[i];
-                d.delta[idx] = x[i];
+                if (j == 0) d.delta[idx] = x[i];
             }
             make_view(e, sview[warp]);
         }
         __syncwarp();
         if (lane < kViewDoubles)
-            reinterpret_cast<double*>(d.views + (long long)(cur ^ 1) * d.M + v)[lane] =
+            reinterpret_cast<double*>(d.views + (long long)tb * d.M + v)[lane] =
                 reinterpret_cast<const double*>(&sview[warp])[lane];
     }
 }

@@ -49,9 +49,9 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned by
 // One warp's sweep over its chunk.  body(point) runs for every point of the current piece owned by
 // this lane; begin / end run once per piece with the warp converged (end after a __syncwarp()).
 // bars: D mbarriers of this warp, used by this sweep only.
-template <int D, int WS, class Begin, class Body, class End>
+template <int D, int WS, int NV, class Begin, class Body, class End>
 __device__ __forceinline__ void sweep_windows(const Dev& d, const Piece* __restrict__ pieces, const WarpRec& rec,
-                                              const ViewC* __restrict__ views, ViewC& sview, PointRing<D, WS>& ring,
+                                              const ViewC* const (&views)[NV], ViewC (&sview)[NV], PointRing<D, WS>& ring,
                                               unsigned long long* bars, int lane, Begin begin, Body body, End end) {
     constexpr int WP = 32 * WS;           // points per window
     const int p0 = rec.p0, p1 = rec.p1;
@@ -81,8 +81,12 @@ __device__ __forceinline__ void sweep_windows(const Dev& d, const Piece* __restr
     }
     __syncwarp();
     Piece cur = rec.first;
-    double vn = 0.0;
-    if (lane < kViewDoubles) vn = reinterpret_cast<const double*>(views + cur.view)[lane];
+    double vn[NV];
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+        vn[j] = 0.0;
+        if (lane < kViewDoubles) vn[j] = reinterpret_cast<const double*>(views[j] + cur.view)[lane];
+    }
     int loaded = -1, ready = -1;          // last 32-point step held in registers; last window waited for
     Pt pt;
     pt.X = pt.Y = pt.Z = pt.U = pt.V = 0.0;
@@ -91,9 +95,15 @@ __device__ __forceinline__ void sweep_windows(const Dev& d, const Piece* __restr
         Piece nxt = cur;
         if (has_next) nxt = pieces[pi + 1];
         __syncwarp();
-        if (lane < kViewDoubles) reinterpret_cast<double*>(&sview)[lane] = vn;
+        if (lane < kViewDoubles) {
+#pragma unroll
+            for (int j = 0; j < NV; ++j) reinterpret_cast<double*>(&sview[j])[lane] = vn[j];
+        }
         __syncwarp();
-        if (has_next && lane < kViewDoubles) vn = reinterpret_cast<const double*>(views + nxt.view)[lane];
+        if (has_next && lane < kViewDoubles) {
+#pragma unroll
+            for (int j = 0; j < NV; ++j) vn[j] = reinterpret_cast<const double*>(views[j] + nxt.view)[lane];
+        }
         begin(cur, pi);
         const int t0 = (cur.start - cs) >> 5, t1 = (cur.start + cur.count - 1 - cs) >> 5;
         for (int t = t0; t <= t1; ++t) {

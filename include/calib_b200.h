@@ -70,6 +70,15 @@ int calib_set_segment(calib_t* h, int points_per_task);
  * CALIB_E_STATE). */
 int calib_set_loop_mode(calib_t* h, int mode);
 
+/* Damping ladder.  After a rejected step the reference multiplies lambda by 10 and tries again from
+ * the same point with the same normal equations (src/calibrate.py:161-166).  The library may take
+ * the next few of those trial steps ahead of the decisions -- one pass of the Schur, back-substitution
+ * and cost kernels for up to max_candidates dampings lambda, 10 lambda, ... (one candidate after an
+ * accepted step, doubling after rejected ones) -- and then replays the reference's accept/reject rule
+ * candidate by candidate.  Iterates, costs, lambdas, trace rows and the iteration count are those of
+ * the one-at-a-time loop, bit for bit; only the number of launches changes.  1, 2 or 4 (default 4). */
+int calib_set_ladder(calib_t* h, int max_candidates);
+
 /* How the trial-cost sweep brings the detections in: 1 = bulk copies (TMA) into a per-warp
  * shared-memory ring, 0 = coalesced loads with register prefetch, -1 (default) = by size (the ring
  * when the detections exceed what L2 keeps between sweeps).  Results are bit-identical. */

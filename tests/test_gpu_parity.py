@@ -273,6 +273,36 @@ def test_loop_modes_identical(golden):
         prob.close()
 
 
+def test_damping_ladder_is_invisible(golden):
+    """Trial steps taken ahead of the accept/reject decisions (calib_set_ladder) change the number of
+    launches and nothing else: traces, iterates and iteration counts are bit-identical to the
+    one-candidate-per-pass loop, in both loop modes and when maxIters cuts a pass short."""
+    for case in ("cfg1", "cfg1n", "itest", "cfg2"):
+        g = golden(case)
+        prob = _problem(g)
+        prob.set_ladder(1)
+        s1, P1, i1, t1 = prob.lm_run(g["P0"], 100)
+        n1 = prob.last_run_stats()[1]
+        for cap in (2, 4):
+            for mode in (1, 2):
+                prob.set_ladder(cap)
+                prob.set_loop_mode(mode)
+                s2, P2, i2, t2 = prob.lm_run(g["P0"], 100)
+                assert i1 == i2 and s1 == s2, (case, cap, mode, i1, i2)
+                assert np.array_equal(t1, t2) and np.array_equal(P1, P2), (case, cap, mode)
+            prob.set_loop_mode(2)
+            assert prob.last_run_stats()[1] <= n1
+        rejected = np.where(t1[:, 3] == 0)[0]
+        cuts = {3, i1 - 1} | ({int(rejected[0]) + 2, int(rejected[0]) + 3} if len(rejected) else set())
+        for cut in sorted(c for c in cuts if 0 < c < i1):
+            prob.set_ladder(1)
+            sa, Pa, ia, ta = prob.lm_run(g["P0"], cut)
+            prob.set_ladder(4)
+            sb, Pb, ib, tb = prob.lm_run(g["P0"], cut)
+            assert ia == ib == cut and sa == sb and np.array_equal(ta, tb) and np.array_equal(Pa, Pb), (case, cut)
+        prob.close()
+
+
 # ---- batch of independent calibrations (BASELINE config 4) -------------------------------------
 def _batch_inputs(n, views=20):
     probs = synth.batch_config(n, views)

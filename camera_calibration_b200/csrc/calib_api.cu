@@ -384,6 +384,9 @@ extern "C" int calib_create(calib_t** out, int model, int64_t M, const int64_t* 
         const size_t o_red = a.reserve<double>(kRedN), o_vtab = a.reserve<double>((size_t)kJMax * M * kVtab);
         const size_t o_et = a.reserve<double>(8), o_delta = a.reserve<double>((size_t)h->K);
         const size_t o_dcs = a.reserve<double>(kJMax * 16);
+#ifdef CALIB_STAMPS
+        const size_t o_stamps = a.reserve<unsigned long long>((size_t)4 * kStampBlocks * 8);
+#endif
         const size_t o_st = a.reserve<LmState>(1);
         constexpr int kTraceIters = 256;
         const size_t o_trace = a.reserve<double>(4 * kTraceIters);
@@ -396,6 +399,9 @@ extern "C" int calib_create(calib_t** out, int model, int64_t M, const int64_t* 
         d.Pbuf = a.at<double>(o_P); d.views = a.at<ViewC>(o_views); d.red = a.at<double>(o_red);
         d.vtab = a.at<double>(o_vtab); d.etrial = a.at<double>(o_et); d.delta = a.at<double>(o_delta);
         d.dcs = a.at<double>(o_dcs);
+#ifdef CALIB_STAMPS
+        d.stamps = a.at<unsigned long long>(o_stamps);
+#endif
         d.st = a.at<LmState>(o_st);
         d.trace = a.at<double>(o_trace);
         h->trace_cap = kTraceIters;
@@ -1315,3 +1321,24 @@ extern "C" int calib_batch_lm_run(calib_batch_t* h, double* P_inout, int maxIter
     }
     return CALIB_OK;
 }
+
+#ifdef CALIB_STAMPS
+// latency-study builds only (not in the header): one pass at P, then the globaltimer stamps
+extern "C" int calib_debug_stamps(calib_t* h, const double* P, double lam, unsigned long long* out) {
+    RC(check_handle(h));
+    h->cur = 0;
+    h->dev.use_cond = 0;
+    RC(upload_to(h, P, 0));
+    RC(push_state(h, lam, 0, 0, 0, 1 << 30));
+    RC(make_views(h, 1));
+    Launcher ln{h, false};
+    for (int rep = 0; rep < 3; ++rep) {
+        if (rep == 2) CUDA_TRY(h, cudaMemsetAsync(h->dev.stamps, 0, (size_t)4 * kStampBlocks * 8 * 8, h->stream));
+        if (h->model == 0) { enqueue_eval<0>(h, ln); enqueue_schur<0>(h, ln, 1); enqueue_backsub<0>(h, ln); enqueue_cost<0>(h, ln, 0); }
+        else { enqueue_eval<1>(h, ln); enqueue_schur<1>(h, ln, 1); enqueue_backsub<1>(h, ln); enqueue_cost<1>(h, ln, 0); }
+    }
+    RC(sync(h));
+    CUDA_TRY(h, cudaMemcpy(out, h->dev.stamps, (size_t)4 * kStampBlocks * 8 * 8, cudaMemcpyDeviceToHost));
+    return CALIB_OK;
+}
+#endif

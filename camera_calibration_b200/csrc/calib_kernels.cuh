@@ -87,6 +87,9 @@ struct Dev {  // everything the kernels need; passed by value
     cudaGraphConditionalHandle cond;      // WHILE node of the whole-loop graph
     int use_cond;
     PeerDev peer;                         // nranks > 1: the kernels all-reduce over peer memory
+#ifdef CALIB_STAMPS
+    unsigned long long* stamps;           // [kernel 4][block kStampBlocks][slot 8] globaltimer (latency study builds only)
+#endif
 };
 
 // ---- slot layouts ---------------------------------------------------------------------------
@@ -101,6 +104,17 @@ template <int L> struct SlotsBD {
 };
 // upper triangle (p <= c) of an L x L symmetric matrix followed by an L vector
 __host__ __device__ constexpr int tri(int L, int p, int c) { return p * L - p * (p - 1) / 2 + (c - p); }
+
+#ifdef CALIB_STAMPS
+constexpr int kStampBlocks = 1280;
+#define STAMP(d, kern, slot)                                                                           \
+    do {                                                                                               \
+        if (threadIdx.x == 0 && blockIdx.x < kStampBlocks)                                             \
+            (d).stamps[((kern) * kStampBlocks + blockIdx.x) * 8 + (slot)] = global_timer_ns();        \
+    } while (0)
+#else
+#define STAMP(d, kern, slot) do {} while (0)
+#endif
 
 struct Pt { double X, Y, Z, U, V; };
 
@@ -177,7 +191,10 @@ __device__ __forceinline__ void accum_BD(const PointOut<MODEL>& o, double (&acc)
 // boundaries, so a load is never waited for inside the FP64 stream.  `begin(piece, index)` runs
 // after the view constants are in sview (warp-synchronised), `body(point)` per point of the
 // lane, `end(piece, index)` with all 32 lanes converged.
-template <int NV, class Begin, class Body, class End>
+// PF: how many 32-point steps ahead the points are fetched inside a piece (1 or 2).  A sweep that is
+// bound by FP64 issue needs 1; the cost sweep has so little arithmetic per point that one step in
+// flight per warp leaves it waiting for L2 (16 warps x 1.3 KB per SM against ~1300 cycles).
+template <int NV, int PF, class Begin, class Body, class End>
 __device__ __forceinline__ void sweep_pieces(const Dev& d, const Piece* __restrict__ pieces, const WarpRec& rec,
                                              const ViewC* const (&views)[NV], ViewC (&sview)[NV], int lane,
                                              Begin begin, Body body, End end) {
@@ -208,11 +225,23 @@ __device__ __forceinline__ void sweep_pieces(const Dev& d, const Piece* __restri
         }
         begin(cur, pi);
         if (lane >= cur.count && has_next && lane < nxt.count) load_point(d, (long long)nxt.start + lane, pn);
-        for (int i = lane; i < cur.count; i += 32) {
-            const Pt p = pn;
-            if (i + 32 < cur.count) load_point(d, (long long)cur.start + i + 32, pn);
-            else if (has_next && lane < nxt.count) load_point(d, (long long)nxt.start + lane, pn);
-            body(p);
+        if constexpr (PF == 1) {
+            for (int i = lane; i < cur.count; i += 32) {
+                const Pt p = pn;
+                if (i + 32 < cur.count) load_point(d, (long long)cur.start + i + 32, pn);
+                else if (has_next && lane < nxt.count) load_point(d, (long long)nxt.start + lane, pn);
+                body(p);
+            }
+        } else {
+            Pt pn2 = pn;
+            if (lane + 32 < cur.count) load_point(d, (long long)cur.start + lane + 32, pn2);
+            for (int i = lane; i < cur.count; i += 32) {
+                const Pt p = pn;
+                pn = pn2;
+                if (i + 64 < cur.count) load_point(d, (long long)cur.start + i + 64, pn2);
+                else if (i + 32 >= cur.count && has_next && lane < nxt.count) load_point(d, (long long)nxt.start + lane, pn);
+                body(p);
+            }
         }
         __syncwarp();
         end(cur, pi);

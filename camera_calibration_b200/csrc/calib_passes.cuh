@@ -17,7 +17,7 @@ constexpr size_t kCostDynSmem = kBlockWarps * sizeof(CostRing);
 
 extern __shared__ __align__(128) unsigned char dyn_smem[];
 
-template <bool TMA, int D, int WS, int NV, class Begin, class Body, class End>
+template <bool TMA, int D, int WS, int NV, int PF, class Begin, class Body, class End>
 __device__ __forceinline__ void sweep(const Dev& d, const Piece* __restrict__ pieces, const WarpRec& rec,
                                       const ViewC* const (&views)[NV], ViewC (&sview)[NV], int warp,
                                       unsigned long long* bars, int lane, Begin begin, Body body, End end) {
@@ -25,7 +25,7 @@ __device__ __forceinline__ void sweep(const Dev& d, const Piece* __restrict__ pi
         PointRing<D, WS>* ring = reinterpret_cast<PointRing<D, WS>*>(dyn_smem);
         sweep_windows<D, WS, NV>(d, pieces, rec, views, sview, ring[warp], bars, lane, begin, body, end);
     } else {
-        sweep_pieces<NV>(d, pieces, rec, views, sview, lane, begin, body, end);
+        sweep_pieces<NV, PF>(d, pieces, rec, views, sview, lane, begin, body, end);
     }
 }
 
@@ -41,6 +41,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
     if (w < d.ev_warps) rec = d.ev_rec[w];
     const LmState* st = d.st;
     if (st->done || !st->need_eval) return;
+    STAMP(d, 0, 0);
     __shared__ double sc[16];
     __shared__ __align__(16) ViewC sview[kBlockWarps][1];
     __shared__ double sred[kBlockWarps][kNA];
@@ -55,7 +56,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
         double acc[kNBD];
 #pragma unroll
         for (int i = 0; i < kNBD; ++i) acc[i] = 0.0;
-        sweep<false, 1, 1, 1>(d, d.ev_piece, rec, views, sview[warp], warp, nullptr, lane,
+        sweep<false, 1, 1, 1, 1>(d, d.ev_piece, rec, views, sview[warp], warp, nullptr, lane,
             [&](const Piece&, int) {},
             [&](const Pt& p) {
                 PointOut<MODEL> o;
@@ -71,13 +72,14 @@ __global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
                 for (int i = 0; i < kNBD; ++i) acc[i] = 0.0;
             });
     }
+    STAMP(d, 0, 1);
     // sweep 2: A, g_c, E -- accumulated over all pieces of the warp, one row per block
     {
         double acc[kNA];
 #pragma unroll
         for (int i = 0; i < kNA; ++i) acc[i] = 0.0;
         double e = 0.0;
-        sweep<false, 1, 1, 1>(d, d.ev_piece, rec, views, sview[warp], warp, nullptr, lane,
+        sweep<false, 1, 1, 1, 1>(d, d.ev_piece, rec, views, sview[warp], warp, nullptr, lane,
             [&](const Piece&, int) {},
             [&](const Pt& p) {
                 PointOut<MODEL> o;
@@ -91,7 +93,9 @@ __global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
         sred[warp][2 * lane + 1] = acc[1];
         if (lane == 0) sE[warp] = e;
     }
+    STAMP(d, 0, 2);
     __syncthreads();
+    STAMP(d, 0, 3);
     if (threadIdx.x < kNA) {
         double s = sred[0][threadIdx.x];
 #pragma unroll
@@ -103,6 +107,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
         for (int k = 1; k < kBlockWarps; ++k) s = __dadd_rn(s, sE[k]);
         d.partE[blockIdx.x] = s;
     }
+    STAMP(d, 0, 4);
 }
 
 // ---- accept / reject, lambda update, termination: src/calibrate.py:155-168 ------------------
@@ -159,7 +164,7 @@ __device__ __forceinline__ void cost_sweep(const Dev& d, const WarpRec& rec, int
     for (int j = 0; j < NJ; ++j) views[j] = d.views + (long long)trial_buf(cur, j) * d.M;
     const ViewC* const (&cviews)[NJ] = views;
     ViewC (&sv)[NJ] = reinterpret_cast<ViewC (&)[NJ]>(sview);
-    sweep<TMA, kCostStages, kWinSteps, NJ>(d, d.co_piece, rec, cviews, sv, warp, bars, lane,
+    sweep<TMA, kCostStages, kWinSteps, NJ, 1>(d, d.co_piece, rec, cviews, sv, warp, bars, lane,
         [&](const Piece&, int) {},
         [&](const Pt& p) {
 #pragma unroll
@@ -192,6 +197,7 @@ __global__ void __launch_bounds__(kBlockThreads, 2) k_cost(Dev d, int fuse_accep
     __shared__ int s_last;
     __shared__ __align__(8) unsigned long long bars[kBlockWarps][kCostStages];
     const int cur = st->cur, J = st->J;
+    STAMP(d, 3, 0);
     if (threadIdx.x < kJMax * 16) {
         const int j = threadIdx.x >> 4, i = threadIdx.x & 15;
         if (j < J && i < L) sc[j][i] = d.Pbuf[(long long)trial_buf(cur, j) * d.K + i];
@@ -203,6 +209,7 @@ __global__ void __launch_bounds__(kBlockThreads, 2) k_cost(Dev d, int fuse_accep
     if (J == 1) cost_sweep<MODEL, TMA, 1>(d, rec, cur, sc, sview[warp], bars[warp], warp, lane, e);
     else if (J == 2) cost_sweep<MODEL, TMA, 2>(d, rec, cur, sc, sview[warp], bars[warp], warp, lane, e);
     else cost_sweep<MODEL, TMA, kJMax>(d, rec, cur, sc, sview[warp], bars[warp], warp, lane, e);
+    STAMP(d, 3, 1);
 #pragma unroll
     for (int j = 0; j < kJMax; ++j) {
         const double s = warp_sum(e[j]);
@@ -222,6 +229,7 @@ __global__ void __launch_bounds__(kBlockThreads, 2) k_cost(Dev d, int fuse_accep
         s_last = (prev == gridDim.x - 1);
     }
     __syncthreads();
+    STAMP(d, 3, 2);
     if (!s_last) return;
     __threadfence();
     if (warp < kJMax) {     // warp j sums column j, fixed order
@@ -243,6 +251,7 @@ __global__ void __launch_bounds__(kBlockThreads, 2) k_cost(Dev d, int fuse_accep
             lm_accept<COND>(d);
         }
     }
+    STAMP(d, 3, 3);
 }
 
 }  // namespace calib

@@ -139,6 +139,7 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
     const int nvb = d.sc_groups;
     const int J = st->J;
     const int cand = blockIdx.x / nvb, grp = blockIdx.x - cand * nvb;
+    STAMP(d, 1, 0);
     if (cand < J) {
         // which entries of W this lane accumulates: e = lane + 32 k  ->  (p, c), c in [p, L]
         int ep[3], ec[3];
@@ -166,6 +167,7 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
                 s0 += __ldcg(row + lane); s1 += __ldcg(row + lane + 32); s2 += __ldcg(row + lane + 64);
             }
             __syncwarp();
+            STAMP(d, 1, 1);
             sv[warp][lane] = s0; sv[warp][lane + 32] = s1; sv[warp][lane + 64] = s2;
             __syncwarp();
             // D' = D + lam diag(D), lower Cholesky, every lane redundantly (registers)
@@ -215,6 +217,7 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
             }
         }
         __syncwarp();
+        STAMP(d, 1, 2);
         sv[warp][lane] = wacc[0]; sv[warp][lane + 32] = wacc[1]; sv[warp][lane + 64] = wacc[2];
         __syncthreads();
         if (tid < kNBD) {
@@ -235,6 +238,7 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
         s_last = (prev == gridDim.x - 1);
     }
     __syncthreads();
+    STAMP(d, 1, 3);
     if (!s_last) return;
     __threadfence();
     {
@@ -249,6 +253,7 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
         sga[warp][lane] = a0; sga[warp][lane + 32] = a1;
         if (lane == 0) sge[warp] = e;
     }
+    STAMP(d, 1, 4);
     for (int j = 0; j < J; ++j) {
         double s0 = 0.0, s1 = 0.0, s2 = 0.0;
 #pragma unroll 4
@@ -288,8 +293,10 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
         return;
     }
     for (int e = tid; e < red_n(J); e += kBlockThreads) d.red[e] = sred[e];
+    STAMP(d, 1, 5);
     if (fuse_solve && warp < J)
         solve_reduced<MODEL>(d, sred + kRedA, sred + red_w(warp), sred[kRedE], warp, lane, LdPlain());
+    STAMP(d, 1, 6);
 }
 
 // reduced solve as its own launch (after the all-reduce when NCCL sums the reduced systems):
@@ -326,6 +333,7 @@ __global__ void __launch_bounds__(kBlockThreads) k_backsub(Dev d) {
     const int j = blockIdx.x / nb, grp = blockIdx.x - j * nb;
     if (j >= J) return;
     const int tb = trial_buf(cur, j);
+    STAMP(d, 2, 0);
     for (int v = grp * kBlockWarps + warp; v < d.M; v += nb * kBlockWarps) {
         double* Pt = d.Pbuf + (long long)tb * d.K;
         const double* vt = d.vtab + ((long long)j * d.M + v) * kVtab;
@@ -369,6 +377,7 @@ __global__ void __launch_bounds__(kBlockThreads) k_backsub(Dev d) {
             reinterpret_cast<double*>(d.views + (long long)tb * d.M + v)[lane] =
                 reinterpret_cast<const double*>(&sview[warp])[lane];
     }
+    STAMP(d, 2, 1);
 }
 
 // ---- parity / debug kernels (not on the timed path) ------------------------------------------

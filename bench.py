@@ -373,6 +373,7 @@ def main():
     ap.add_argument("--cpu-sample", type=int, default=512)
     ap.add_argument("--ladder", type=int, default=4, choices=[1, 2, 4],
                     help="damping ladder: trial steps taken ahead of the accept/reject decisions (1 = off)")
+    ap.add_argument("--pdl", type=int, default=0, choices=[0, 1], help="programmatic dependent launch inside the graphs")
     ap.add_argument("--transport", default="auto", choices=["auto", "peer", "nccl"],
                     help="sharded views: in-kernel all-reduce over NVLink peer memory, or NCCL all-reduces")
     args = ap.parse_args()
@@ -410,6 +411,7 @@ def main():
     if args.loop_mode:
         prob.set_loop_mode(args.loop_mode)
     prob.set_ladder(args.ladder)
+    prob.set_pdl(args.pdl)
     transport = "none"
     if world > 1:
         from camera_calibration_b200 import sharding
@@ -453,6 +455,7 @@ def main():
         if world > 1:
             p2.comm_share(prob)
         p2.set_ladder(args.ladder)
+        p2.set_pdl(args.pdl)
         _, _, it, _ = p2.lm_run(Ploc, MAX_ITERS, want_trace=False)
         p2.close()
         return it

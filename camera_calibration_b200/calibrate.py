@@ -142,6 +142,9 @@ class Problem:
         """damping ladder: trial steps taken ahead of the accept/reject decisions (1 = off, 2, 4)"""
         self._check(self._L.calib_set_ladder(self._h, int(max_candidates)))
 
+    def set_pdl(self, on):
+        self._check(self._L.calib_set_pdl(self._h, 1 if on else 0))
+
     def set_loop_mode(self, mode):
         """0 auto, 1 host-driven iteration graphs, 2 device-driven WHILE graph."""
         self._check(self._L.calib_set_loop_mode(self._h, int(mode)))

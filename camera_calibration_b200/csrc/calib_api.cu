@@ -82,6 +82,8 @@ struct calib_handle {
     bool comm_owned = false;
     int nranks = 1, rank = 0;
     std::shared_ptr<PeerComm> peer;        // in-kernel exchange over NVLink peer memory
+    int pdl = 0;                           // programmatic dependent launch between the kernels of the iteration (measured: no gain, off)
+    bool pdl_now = false;                  // set while the iteration is being captured into a graph
     int ladder = kJMax;                    // cap of the damping ladder (1 = one candidate per pass)
     int transport = 0;                     // 0 auto (peer memory when attached, else NCCL), 1 NCCL, 2 peer memory
     double* l2buf = nullptr;
@@ -383,7 +385,7 @@ extern "C" int calib_create(calib_t** out, int model, int64_t M, const int64_t* 
         const size_t o_P = a.reserve<double>((size_t)kNBuf * h->K), o_views = a.reserve<ViewC>((size_t)kNBuf * M);
         const size_t o_red = a.reserve<double>(kRedN), o_vtab = a.reserve<double>((size_t)kJMax * M * kVtab);
         const size_t o_et = a.reserve<double>(8), o_delta = a.reserve<double>((size_t)h->K);
-        const size_t o_dcs = a.reserve<double>(kJMax * 16);
+        const size_t o_dcs = a.reserve<double>(kJMax * 16), o_redA = a.reserve<double>(kRedW0);
 #ifdef CALIB_STAMPS
         const size_t o_stamps = a.reserve<unsigned long long>((size_t)4 * kStampBlocks * 8);
 #endif
@@ -398,7 +400,7 @@ extern "C" int calib_create(calib_t** out, int model, int64_t M, const int64_t* 
         d.X = soa; d.Y = soa + n; d.Z = soa + 2 * n; d.U = soa + 3 * n; d.V = soa + 4 * n;
         d.Pbuf = a.at<double>(o_P); d.views = a.at<ViewC>(o_views); d.red = a.at<double>(o_red);
         d.vtab = a.at<double>(o_vtab); d.etrial = a.at<double>(o_et); d.delta = a.at<double>(o_delta);
-        d.dcs = a.at<double>(o_dcs);
+        d.dcs = a.at<double>(o_dcs); d.redA = a.at<double>(o_redA);
 #ifdef CALIB_STAMPS
         d.stamps = a.at<unsigned long long>(o_stamps);
 #endif
@@ -457,6 +459,13 @@ extern "C" int calib_set_loop_mode(calib_t* h, int mode) {
     return CALIB_OK;
 }
 
+extern "C" int calib_set_pdl(calib_t* h, int on) {
+    if (!h) return fail(nullptr, CALIB_E_ARG, "NULL handle");
+    h->pdl = on ? 1 : 0;
+    drop_graph(h);
+    return CALIB_OK;
+}
+
 extern "C" int calib_set_ladder(calib_t* h, int max_candidates) {
     if (!h) return fail(nullptr, CALIB_E_ARG, "NULL handle");
     if (max_candidates != 1 && max_candidates != 2 && max_candidates != kJMax)
@@ -488,6 +497,26 @@ namespace {
 
 enum { KEVAL = 0, KSCHUR = 1, KBACK = 2, KCOST = 3, KSOLVE = 4 };
 
+// Kernel launch of the iteration.  With h->pdl_now the launch carries the programmatic-dependent-launch
+// attribute: under stream capture the edge to the previous kernel node becomes a programmatic one, the
+// blocks of this kernel are scheduled while the previous kernel drains (every kernel of the iteration
+// triggers its dependents at its top and waits with griddepcontrol.wait before it reads anything the
+// previous kernel wrote), and the ~3 us between two dependent kernel nodes shrinks.
+template <typename... KArgs, typename... Args>
+cudaError_t launch_iter(calib_handle* h, void (*kern)(KArgs...), int grid, int block, size_t smem, Args... args) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof cfg);
+    cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3((unsigned)block);
+    cfg.dynamicSmemBytes = smem; cfg.stream = h->stream;
+    cudaLaunchAttribute at[1];
+    if (h->pdl_now) {
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+    }
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
 struct Launcher {
     calib_handle* h;
     bool prof;
@@ -509,7 +538,7 @@ void enqueue_eval(calib_handle* h, Launcher& ln) {
     const Dev& d = h->dev;
     cudaEvent_t a, b;
     ln.begin(&a, &b);
-    k_eval<MODEL><<<d.ev_blocks, kBlockThreads, 0, h->stream>>>(d);
+    launch_iter(h, k_eval<MODEL>, d.ev_blocks, kBlockThreads, 0, d);
     ln.end(KEVAL, a, b);
     ln.count += 1;
 }
@@ -519,7 +548,7 @@ void enqueue_schur(calib_handle* h, Launcher& ln, int fuse_solve) {
     const Dev& d = h->dev;
     cudaEvent_t a, b;
     ln.begin(&a, &b);
-    k_schur<MODEL><<<d.sc_groups * kJMax, kBlockThreads, 0, h->stream>>>(d, fuse_solve);
+    launch_iter(h, k_schur<MODEL>, d.sc_groups * kJMax, kBlockThreads, 0, d, fuse_solve);
     ln.end(KSCHUR, a, b);
     ln.count += 1;
 }
@@ -538,7 +567,7 @@ void enqueue_backsub(calib_handle* h, Launcher& ln) {
     const Dev& d = h->dev;
     cudaEvent_t a, b;
     ln.begin(&a, &b);
-    k_backsub<MODEL><<<d.bs_groups * kJMax, kBlockThreads, 0, h->stream>>>(d);
+    launch_iter(h, k_backsub<MODEL>, d.bs_groups * kJMax, kBlockThreads, 0, d);
     ln.end(KBACK, a, b);
     ln.count += 1;
 }
@@ -551,11 +580,11 @@ void enqueue_cost(calib_handle* h, Launcher& ln, int fuse_accept) {
     // bulk-copy ring when the detections cannot stay in L2 between the sweeps, plain loads otherwise
     const bool tma = h->cost_tma >= 0 ? h->cost_tma != 0 : (size_t)h->N * 40 > ((size_t)96 << 20);
     if (tma) {
-        if (d.use_cond) k_cost<MODEL, true, true><<<d.co_blocks, kBlockThreads, kCostDynSmem, h->stream>>>(d, fuse_accept);
-        else k_cost<MODEL, false, true><<<d.co_blocks, kBlockThreads, kCostDynSmem, h->stream>>>(d, fuse_accept);
+        if (d.use_cond) launch_iter(h, k_cost<MODEL, true, true>, d.co_blocks, kBlockThreads, kCostDynSmem, d, fuse_accept);
+        else launch_iter(h, k_cost<MODEL, false, true>, d.co_blocks, kBlockThreads, kCostDynSmem, d, fuse_accept);
     } else {
-        if (d.use_cond) k_cost<MODEL, true, false><<<d.co_blocks, kBlockThreads, 0, h->stream>>>(d, fuse_accept);
-        else k_cost<MODEL, false, false><<<d.co_blocks, kBlockThreads, 0, h->stream>>>(d, fuse_accept);
+        if (d.use_cond) launch_iter(h, k_cost<MODEL, true, false>, d.co_blocks, kBlockThreads, 0, d, fuse_accept);
+        else launch_iter(h, k_cost<MODEL, false, false>, d.co_blocks, kBlockThreads, 0, d, fuse_accept);
     }
     ln.end(KCOST, a, b);
     ln.count += 1;
@@ -617,7 +646,9 @@ int build_graph(calib_handle* h) {
     h->dev.use_cond = 0;
     CUDA_TRY(h, cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
     Launcher ln{h, false};
+    h->pdl_now = h->pdl != 0 && !nccl_active(h);
     int rc = enqueue_iteration_any(h, ln);
+    h->pdl_now = false;
     cudaError_t e = cudaStreamEndCapture(h->stream, &g);
     if (rc) { if (g) cudaGraphDestroy(g); return rc; }
     CUDA_TRY(h, e);
@@ -652,7 +683,9 @@ int build_loop_graph(calib_handle* h) {
     e = cudaStreamBeginCaptureToGraph(h->stream, body, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal);
     if (e != cudaSuccess) { h->dev.use_cond = 0; cudaGraphDestroy(g); CUDA_TRY(h, e); }
     Launcher ln{h, false};
+    h->pdl_now = h->pdl != 0 && !nccl_active(h);
     int rc = enqueue_iteration_any(h, ln);
+    h->pdl_now = false;
     cudaGraph_t got = nullptr;
     e = cudaStreamEndCapture(h->stream, &got);
     h->dev.use_cond = 0;
@@ -743,7 +776,16 @@ extern "C" int calib_lm_run_resident(calib_t* h, int maxIters, double lam0, doub
         return fail(h, CALIB_E_STATE, "loop mode 2: a WHILE-node body cannot hold NCCL nodes (cudaGraphInstantiate rejects "
                                       "them); use the peer-memory transport (calib_peer_attach) or loop mode 1");
     const bool device_loop = !prof && (h->loop_mode == 2 || (h->loop_mode == 0 && !nccl_active(h)));
-    if (!prof) RC(device_loop ? build_loop_graph(h) : build_graph(h));
+    if (!prof) {
+        int rc = device_loop ? build_loop_graph(h) : build_graph(h);
+        if (rc && h->pdl) {          // a driver that rejects programmatic edges here: plain edges
+            h->pdl = 0;
+            cudaGetLastError();
+            drop_graph(h);
+            rc = device_loop ? build_loop_graph(h) : build_graph(h);
+        }
+        RC(rc);
+    }
     for (auto& pe : h->prof_events) { cudaEventDestroy(pe.second.first); cudaEventDestroy(pe.second.second); }
     h->prof_events.clear();
     for (int i = 0; i < 5; ++i) { h->ktime[i] = 0; h->kcount[i] = 0; }

@@ -53,7 +53,7 @@ struct LmState {
     int comm_fail;         // a peer never arrived at an exchange (calib_peer.cuh)
     int J, jmax;           // candidates of this pass of the damping ladder; its cap (1 = ladder off)
     int n_pass;            // passes (one k_schur/k_backsub/k_cost each) so far
-    unsigned int cnt_schur, cnt_cost;
+    unsigned int cnt_schur, cnt_cost, cnt_eval, pad1;
     long long n_eval;   // Jacobian evaluations actually executed
 };
 
@@ -77,6 +77,7 @@ struct Dev {  // everything the kernels need; passed by value
     double* partBD;                       // ev_pieces x kNBD
     double* partW;                        // kJMax x sc_groups x kNBD
     double* red;                          // kRedN : the reduced system, all-reduced when sharded
+    double* redA;                         // kRedW0: A slots, g_c and the cost of THIS rank at the current point
     double* vtab;                         // kJMax x M x kVtab
     double* partC;                        // co_blocks x kJMax (trial costs)
     double* etrial;                       // kJMax
@@ -115,6 +116,10 @@ constexpr int kStampBlocks = 1280;
 #else
 #define STAMP(d, kern, slot) do {} while (0)
 #endif
+
+// Programmatic dependent launch (see launch_iter in calib_api.cu): no-ops without the launch attribute.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 struct Pt { double X, Y, Z, U, V; };
 

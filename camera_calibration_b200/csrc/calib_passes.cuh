@@ -38,7 +38,9 @@ __global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
     const int w = blockIdx.x * kBlockWarps + warp;
     WarpRec rec;                       // issued together with the state load below: one round trip
     rec.p0 = rec.p1 = 0;
-    if (w < d.ev_warps) rec = d.ev_rec[w];
+    pdl_trigger();
+    if (w < d.ev_warps) rec = d.ev_rec[w];        // static: may be read before the previous kernel is done
+    pdl_wait();
     const LmState* st = d.st;
     if (st->done || !st->need_eval) return;
     STAMP(d, 0, 0);
@@ -46,6 +48,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
     __shared__ __align__(16) ViewC sview[kBlockWarps][1];
     __shared__ double sred[kBlockWarps][kNA];
     __shared__ double sE[kBlockWarps];
+    __shared__ int s_last;
     const int cur = st->cur;
     const double* P = d.Pbuf + (long long)cur * d.K;
     const ViewC* const views[1] = {d.views + (long long)cur * d.M};
@@ -107,6 +110,52 @@ __global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
         for (int k = 1; k < kBlockWarps; ++k) s = __dadd_rn(s, sE[k]);
         d.partE[blockIdx.x] = s;
     }
+    // The last block to finish sums the block rows (fixed order) into redA: the intrinsic block and
+    // the cost do not change while steps from this point are rejected, so this is paid once per
+    // evaluation and k_schur reads 65 numbers instead of 148 rows on every pass.
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned int prev = atomicAdd(&d.st->cnt_eval, 1u);
+        s_last = (prev == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    {
+        constexpr int R = 19;                       // rows per warp held in flight (148 blocks / 8 warps)
+        double a0 = 0.0, a1 = 0.0, e = 0.0;
+        for (int r0 = warp; r0 < d.ev_blocks; r0 += kBlockWarps * R) {
+            double t0[R], t1[R];
+#pragma unroll
+            for (int k = 0; k < R; ++k) {
+                const int r = r0 + k * kBlockWarps;
+                const double* row = d.partA + (long long)r * kNA;
+                t0[k] = r < d.ev_blocks ? __ldcg(row + lane) : 0.0;
+                t1[k] = r < d.ev_blocks ? __ldcg(row + lane + 32) : 0.0;
+            }
+#pragma unroll
+            for (int k = 0; k < R; ++k) { a0 += t0[k]; a1 += t1[k]; }
+        }
+        for (int r = threadIdx.x; r < d.ev_blocks; r += kBlockThreads) e = __dadd_rn(e, __ldcg(d.partE + r));
+        e = warp_sum(e);
+        sred[warp][lane] = a0; sred[warp][lane + 32] = a1;
+        if (lane == 0) sE[warp] = e;
+    }
+    __syncthreads();
+    if (threadIdx.x < kNA) {
+        double s = sred[0][threadIdx.x];
+#pragma unroll
+        for (int k = 1; k < kBlockWarps; ++k) s += sred[k][threadIdx.x];
+        d.redA[kRedA + threadIdx.x] = s;
+    } else if (threadIdx.x == kNA) {
+        double s = sE[0];
+#pragma unroll
+        for (int k = 1; k < kBlockWarps; ++k) s = __dadd_rn(s, sE[k]);
+        d.redA[kRedE] = s;
+        d.st->cnt_eval = 0;
+        d.st->n_eval += 1;
+    }
     STAMP(d, 0, 4);
 }
 
@@ -150,6 +199,7 @@ __device__ __forceinline__ void lm_accept(const Dev& d) {
 
 template <bool COND>
 __global__ void k_accept(Dev d) {
+    pdl_wait();
     if (d.st->done) return;
     lm_accept<COND>(d);
 }
@@ -184,7 +234,9 @@ __global__ void __launch_bounds__(kBlockThreads, 2) k_cost(Dev d, int fuse_accep
     const int w = blockIdx.x * kBlockWarps + warp;
     WarpRec rec;
     rec.p0 = rec.p1 = 0;
+    pdl_trigger();
     if (w < d.co_warps) rec = d.co_rec[w];
+    pdl_wait();
     LmState* st = d.st;
     if (st->done) {   // also after a failed exchange: the WHILE node must not spin
         if (COND) { if (blockIdx.x == 0 && threadIdx.x == 0) cudaGraphSetConditional(d.cond, 0u); }

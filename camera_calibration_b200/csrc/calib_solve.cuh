@@ -97,25 +97,104 @@ __device__ __forceinline__ double solve_reduced_core(const double* redA, const d
     return rhs;
 }
 
-// E: the cost at the current point as the evaluation pass summed it.  It seeds the loop; from the
-// second iteration on the current cost IS the trial cost of the last accepted step (set by
-// lm_accept), as in the reference where both numbers come from one function (calibrate.py:155-156).
-// j: candidate of the damping ladder (lam * 10^j, trial buffer j).
-template <int MODEL, class Ld>
-__device__ __forceinline__ void solve_reduced(const Dev& d, const double* redA, const double* redW, double E,
-                                              int j, int lane, Ld ld) {
-    constexpr int L = ModelTraits<MODEL>::L;
-    LmState* st = d.st;
-    double lam = st->lam;
-    for (int k = 0; k < j; ++k) lam = lam * 10.0;      // the reference's own update chain
-    const double dc = solve_reduced_core<MODEL>(redA, redW, lam, lane, ld);
-    const int cur = st->cur;
-    if (lane < L) {
-        if (j == 0) d.delta[lane] = dc;
-        d.dcs[j * 16 + lane] = dc;
-        d.Pbuf[(long long)trial_buf(cur, j) * d.K + lane] = d.Pbuf[(long long)cur * d.K + lane] + dc;
+// ---- the same solve for the large path, with everything that is not the serial chain taken off it ----
+// One warp: Cholesky solve of the dense system (same operations, same order as
+// solve_reduced_core); the factor goes back to shared memory so that the back-substitution reads
+// L[j][i] instead of shuffling whole rows.  Returns dc[lane] for lane < L.
+template <int L>
+__device__ __forceinline__ double solve_dense_core(double* S, int lane) {
+    const int i = lane < L ? lane : L - 1;       // idle lanes mirror the last row (no divergence)
+    double row[L];
+#pragma unroll
+    for (int j = 0; j < L; ++j) row[j] = S[i * L + j];
+    double rhs = S[L * L + i];
+    double inv[L];
+#pragma unroll
+    for (int j = 0; j < L; ++j) {
+        const double dj = __shfl_sync(0xffffffffu, row[j], j);
+        const double id = rsqrt(dj);             // dj <= 0 or NaN poisons the step (rejected)
+        inv[j] = id;
+        const double lij = row[j] * id;
+        row[j] = lij;
+#pragma unroll
+        for (int k = 0; k < L; ++k) {
+            if (k > j) {
+                const double lkj = __shfl_sync(0xffffffffu, lij, k);
+                row[k] = fma(-lij, lkj, row[k]);
+            }
+        }
     }
-    if (j == 0 && lane == 0 && st->iter == 0) st->E_cur = E;
+    __syncwarp();
+    if (lane < L) {
+#pragma unroll
+        for (int j = 0; j < L; ++j) S[i * L + j] = row[j];
+    }
+    __syncwarp();
+#pragma unroll
+    for (int j = 0; j < L; ++j) {
+        const double yj = __shfl_sync(0xffffffffu, rhs * inv[j], j);
+        if (i == j) rhs = yj;
+        else if (i > j) rhs = fma(-row[j], yj, rhs);
+    }
+#pragma unroll
+    for (int j = L - 1; j >= 0; --j) {
+        const double xj = __shfl_sync(0xffffffffu, rhs * inv[j], j);
+        const double mine = S[j * L + i];        // L[j][i]
+        if (i == j) rhs = xj;
+        else if (i < j) rhs = fma(-mine, xj, rhs);
+    }
+    return rhs;
+}
+
+// Called by a whole block after red (shared or global, layout of red[]) is final: builds the dense
+// systems of the J candidates with all threads, then warp j solves candidate j and writes the step
+// and the trial shared parameters.  E seeds the loop (see lm_accept): from the second iteration on
+// the current cost IS the trial cost of the last accepted step, as in the reference where both
+// numbers come from one function (calibrate.py:155-156).
+template <int MODEL, class Ld>
+__device__ __forceinline__ void solve_candidates(const Dev& d, const double* red, double* dense, int J, Ld ld) {
+    constexpr int L = ModelTraits<MODEL>::L, NE = L * L + L;
+    LmState* st = d.st;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const double lam0 = st->lam;
+    const int cur = st->cur, iter = st->iter;
+    double pcur = 0.0;
+    if (warp < J && lane < L) pcur = d.Pbuf[(long long)cur * d.K + lane];
+    for (int e = tid; e < J * NE; e += (int)blockDim.x) {
+        const int j = e / NE;
+        double lam = lam0;
+        for (int k = 0; k < j; ++k) lam = lam * 10.0;      // the reference's own update chain
+        // red may be global (NCCL path): go through ld
+        const int el = e - j * NE;
+        using T = ModelTraits<MODEL>;
+        constexpr int ND = T::ND;
+        using SA = SlotsA<ND>;
+        const double* redA = red + kRedA;
+        const double* redW = red + red_w(j);
+        double out;
+        if (el < L * L) {
+            const int i = el / L, c = el - i * L;
+            const int lo = i < c ? i : c, hi = i < c ? c : i;
+            const int sl = a_slot<ND>(lo, hi);
+            double v = sl >= 0 ? ld(redA + sl) : 0.0;
+            if (i == c) v = fma(lam, v, v);
+            out = v - ld(redW + tri(L, lo, hi));
+        } else {
+            const int i = el - L * L;
+            out = ld(redA + SA::G + i) - ld(redW + L * (L + 1) / 2 + i);
+        }
+        dense[e] = out;
+    }
+    __syncthreads();
+    if (warp < J) {
+        const double dc = solve_dense_core<L>(dense + warp * NE, lane);
+        if (lane < L) {
+            if (warp == 0) d.delta[lane] = dc;
+            d.dcs[warp * 16 + lane] = dc;
+            d.Pbuf[(long long)trial_buf(cur, warp) * d.K + lane] = pcur + dc;
+        }
+        if (warp == 0 && lane == 0 && iter == 0) st->E_cur = ld(red + kRedE);
+    }
 }
 
 // ---- per-view Schur stage -------------------------------------------------------------------------
@@ -127,13 +206,15 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
     using T = ModelTraits<MODEL>;
     constexpr int L = T::L, NZ = L + 1, NT = L * (L + 1) / 2, NW = NT + L;
     using S = SlotsBD<L>;
+    pdl_trigger();
+    pdl_wait();
     LmState* st = d.st;
     if (st->done) return;
     __shared__ double sv[kBlockWarps][kNBD];       // the view's summed piece rows; reused for sums
     __shared__ double sz[kBlockWarps][NZ * 6];     // Z = L^-1 [B^T | g_v], column-major by c
     __shared__ double sl[kBlockWarps][24];         // packed lower factor of the view block
-    __shared__ double sga[kBlockWarps][kNA], sge[kBlockWarps];
     __shared__ double sred[kRedN];                 // the reduced system in the layout of red[]
+    __shared__ double sdense[kJMax * (L * L + L)];  // its dense form, per candidate
     __shared__ int s_last;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nvb = d.sc_groups;
@@ -241,25 +322,26 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
     STAMP(d, 1, 3);
     if (!s_last) return;
     __threadfence();
-    {
-        double a0 = 0.0, a1 = 0.0, e = 0.0;
-#pragma unroll 4
-        for (int r = warp; r < d.ev_blocks; r += kBlockWarps) {
-            const double* row = d.partA + (long long)r * kNA;
-            a0 += __ldcg(row + lane); a1 += __ldcg(row + lane + 32);
-        }
-        for (int r = tid; r < d.ev_blocks; r += kBlockThreads) e = __dadd_rn(e, __ldcg(d.partE + r));
-        e = warp_sum(e);
-        sga[warp][lane] = a0; sga[warp][lane + 32] = a1;
-        if (lane == 0) sge[warp] = e;
-    }
+    // the intrinsic block, g_c and the cost at the current point, as k_eval's last block left them
+    if (tid < kRedW0) sred[tid] = tid <= kRedE ? __ldcg(d.redA + tid) : 0.0;
+    if (tid == 0) st->cnt_schur = 0;
     STAMP(d, 1, 4);
     for (int j = 0; j < J; ++j) {
+        constexpr int R = 8;                        // rows per warp held in flight
         double s0 = 0.0, s1 = 0.0, s2 = 0.0;
-#pragma unroll 4
-        for (int r = warp; r < nvb; r += kBlockWarps) {
-            const double* row = d.partW + ((long long)j * nvb + r) * kNBD;
-            s0 += __ldcg(row + lane); s1 += __ldcg(row + lane + 32); s2 += __ldcg(row + lane + 64);
+        for (int r0 = warp; r0 < nvb; r0 += kBlockWarps * R) {
+            double t0[R], t1[R], t2[R];
+#pragma unroll
+            for (int k = 0; k < R; ++k) {
+                const int r = r0 + k * kBlockWarps;
+                const double* row = d.partW + ((long long)j * nvb + r) * kNBD;
+                const bool in = r < nvb;
+                t0[k] = in ? __ldcg(row + lane) : 0.0;
+                t1[k] = in ? __ldcg(row + lane + 32) : 0.0;
+                t2[k] = in ? __ldcg(row + lane + 64) : 0.0;
+            }
+#pragma unroll
+            for (int k = 0; k < R; ++k) { s0 += t0[k]; s1 += t1[k]; s2 += t2[k]; }
         }
         __syncthreads();          // sv of the previous candidate has been consumed
         sv[warp][lane] = s0; sv[warp][lane + 32] = s1; sv[warp][lane + 64] = s2;
@@ -271,21 +353,6 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
             sred[red_w(j) + tid] = s;
         }
     }
-    if (tid < kNA) {
-        double s = sga[0][tid];
-#pragma unroll
-        for (int k = 1; k < kBlockWarps; ++k) s += sga[k][tid];
-        sred[kRedA + tid] = s;
-    } else if (tid == kNA) {
-        double s = sge[0];
-#pragma unroll
-        for (int k = 1; k < kBlockWarps; ++k) s = __dadd_rn(s, sge[k]);
-        sred[kRedE] = s;
-        st->cnt_schur = 0;
-        if (st->need_eval) st->n_eval += 1;
-    } else if (tid < kRedW0) {
-        sred[tid] = 0.0;
-    }
     __syncthreads();
     // views sharded over the GPUs of the node: sum the reduced systems of all ranks, right here
     if (d.peer.nranks > 1 && !peer_allreduce(d.peer, 0, sred, red_n(J), &s_last)) {
@@ -294,8 +361,7 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
     }
     for (int e = tid; e < red_n(J); e += kBlockThreads) d.red[e] = sred[e];
     STAMP(d, 1, 5);
-    if (fuse_solve && warp < J)
-        solve_reduced<MODEL>(d, sred + kRedA, sred + red_w(warp), sred[kRedE], warp, lane, LdPlain());
+    if (fuse_solve) solve_candidates<MODEL>(d, sred, sdense, J, LdPlain());
     STAMP(d, 1, 6);
 }
 
@@ -303,10 +369,11 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
 // one warp per candidate
 template <int MODEL>
 __global__ void k_solve(Dev d) {
+    constexpr int L = ModelTraits<MODEL>::L;
+    pdl_wait();
     if (d.st->done) return;
-    const int j = threadIdx.x >> 5;
-    if (j < d.st->J)
-        solve_reduced<MODEL>(d, d.red + kRedA, d.red + red_w(j), __ldcg(d.red + kRedE), j, threadIdx.x & 31, LdCg());
+    __shared__ double sdense[kJMax * (L * L + L)];
+    solve_candidates<MODEL>(d, d.red, sdense, d.st->J, LdCg());
 }
 
 // ---- back-substitution, trial parameters and trial view constants: one warp per view; grid =
@@ -315,6 +382,8 @@ template <int MODEL>
 __global__ void __launch_bounds__(kBlockThreads) k_backsub(Dev d) {
     using T = ModelTraits<MODEL>;
     constexpr int L = T::L;
+    pdl_trigger();
+    pdl_wait();
     LmState* st = d.st;
     if (st->done) return;
     __shared__ double srow[kBlockWarps][kVtab];

@@ -109,6 +109,8 @@ def lib():
         "calib_time_kernel": (c_int, [_vp, _d, c_dbl, c_int, c_int, c_int, _d]),
         "calib_measure_fp64_peak": (c_int, [c_int, _d]),
         "calib_flush_l2": (c_int, [_vp]),
+        "calib_refine_homographies": (c_int, [_vp, _d, c_int, c_dbl, c_dbl, c_dbl, c_dbl,
+                                              ctypes.POINTER(c_int), _d]),
         "calib_comm_unique_id": (c_int, [_vp]),
         "calib_comm_init": (c_int, [_vp, c_int, c_int, _vp]),
         "calib_comm_share": (c_int, [_vp, _vp]),

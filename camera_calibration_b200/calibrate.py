@@ -260,6 +260,21 @@ class Problem:
     def comm_share(self, owner):
         self._check(self._L.calib_comm_share(self._h, owner._h))
 
+    def refine_homographies(self, H, maxIters=20, lam0=1e-3, lam_min=1e-10, lam_max=1e10, err_min=1e-12,
+                            want_trace=False):
+        """Calibrator._refineHomographies on the handle's detections (src/calibrate.py:60-115).
+        H: (M, 9) | (M, 3, 3) initial homographies -> (Href (M, 3, 3), iters (M,), trace | None)"""
+        Hb = np.array(H, dtype=np.float64).reshape(-1, 9).copy()
+        M = self.M
+        if Hb.shape[0] != M:
+            raise ValueError("expected %d homographies, got %d" % (M, Hb.shape[0]))
+        iters = np.zeros(M, dtype=np.int32)
+        trace = np.zeros((M, int(maxIters), 4)) if want_trace else None
+        self._check(self._L.calib_refine_homographies(
+            self._h, dptr(Hb), int(maxIters), float(lam0), float(lam_min), float(lam_max), float(err_min),
+            iters.ctypes.data_as(ctypes.POINTER(ctypes.c_int)), dptr(trace) if want_trace else None))
+        return Hb.reshape(M, 3, 3), iters, trace
+
     def peer_export(self) -> bytes:
         """64-byte CUDA IPC handle of this rank's inbox for the in-kernel all-reduce"""
         buf = ctypes.create_string_buffer(64)
@@ -427,6 +442,22 @@ class Calibrator:
         raise NotImplementedError(
             "the linear initial estimate (src/calibrate.py:41-58) is not part of the GPU path; "
             "use the reference's Calibrator.estimateCalibrationParameters and pass its result")
+
+    def _refineHomographies(self, Hs, allDetections):
+        """src/calibrate.py:60-68: per-view LM refinement of the DLT homographies, all views in one
+        launch (calib_refine_homographies).  Returns a list of (3,3) arrays like the reference."""
+        prob = Problem.from_detections(self._model, allDetections, self._device)
+        try:
+            Href, iters, _ = prob.refine_homographies(np.array([np.asarray(H).ravel() for H in Hs]), 20,
+                                                      1e-3, self._λmin, self._λmax, self._Pt_error_min)
+        finally:
+            prob.close()
+        self.lastHomographyIters = iters
+        return [Href[i] for i in range(len(Href))]
+
+    def _refineHomography(self, H, sensorPoints, modelPoints, jac=None):
+        """src/calibrate.py:70-110 for one view."""
+        return self._refineHomographies([H], [(sensorPoints, modelPoints)])[0]
 
     def refineCalibrationParameters(self, Ainitial, Winitial, kInitial, allDetections,
                                     maxIters, shouldPrint=False):

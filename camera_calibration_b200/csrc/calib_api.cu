@@ -17,6 +17,7 @@
 #include "../../include/calib_b200.h"
 #include "calib_solve.cuh"
 #include "calib_batch.cuh"
+#include "calib_homography.cuh"
 
 using namespace calib;
 
@@ -1190,6 +1191,43 @@ extern "C" int calib_set_transport(calib_t* h, int mode) {
 extern "C" int calib_transport(const calib_t* h) {
     if (!h) return -1;
     return peer_active(h) ? 2 : (h->comm ? 1 : 0);
+}
+
+// ---- per-view homography refinement (calib_homography.cuh) -------------------------------------------
+extern "C" int calib_refine_homographies(calib_t* h, double* H_inout, int maxIters, double lam0, double lam_min,
+                                         double lam_max, double err_min, int* iters_out, double* trace) {
+    RC(check_handle(h));
+    if (!H_inout) return fail(h, CALIB_E_ARG, "calib_refine_homographies: H is NULL");
+    if (maxIters <= 0) return fail(h, CALIB_E_ARG, "calib_refine_homographies: maxIters <= 0");
+    const size_t M = (size_t)h->M;
+    std::vector<void*> tmp;
+    long long* d_offs = nullptr;
+    double *d_H = nullptr, *d_tr = nullptr;
+    int* d_it = nullptr;
+    int rc = [&]() -> int {
+        CUDA_TRY(h, dalloc(tmp, &d_offs, M + 1));
+        CUDA_TRY(h, dalloc(tmp, &d_H, M * 9));
+        CUDA_TRY(h, dalloc(tmp, &d_it, M));
+        if (trace) CUDA_TRY(h, dalloc(tmp, &d_tr, M * (size_t)maxIters * 4));
+        static_assert(sizeof(long long) == sizeof(int64_t), "int64 layout");
+        CUDA_TRY(h, cudaMemcpyAsync(d_offs, h->view_offsets.data(), (M + 1) * 8, cudaMemcpyHostToDevice, h->stream));
+        CUDA_TRY(h, cudaMemcpyAsync(d_H, H_inout, M * 72, cudaMemcpyHostToDevice, h->stream));
+        if (trace) CUDA_TRY(h, cudaMemsetAsync(d_tr, 0, M * (size_t)maxIters * 32, h->stream));
+        HomDev d;
+        d.X = h->dev.X; d.Y = h->dev.Y; d.U = h->dev.U; d.V = h->dev.V;
+        d.offs = d_offs; d.M = (int)M; d.max_iters = maxIters; d.want_trace = trace ? 1 : 0;
+        d.lam0 = lam0; d.lam_min = lam_min; d.lam_max = lam_max; d.err_min = err_min;
+        d.H = d_H; d.iters = d_it; d.trace = d_tr;
+        const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>(((int64_t)M + kBlockWarps - 1) / kBlockWarps, 8 * h->n_sm));
+        k_homography_lm<<<blocks, kBlockThreads, 0, h->stream>>>(d);
+        CUDA_TRY(h, cudaGetLastError());
+        CUDA_TRY(h, cudaMemcpyAsync(H_inout, d_H, M * 72, cudaMemcpyDeviceToHost, h->stream));
+        if (iters_out) CUDA_TRY(h, cudaMemcpyAsync(iters_out, d_it, M * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+        if (trace) CUDA_TRY(h, cudaMemcpyAsync(trace, d_tr, M * (size_t)maxIters * 32, cudaMemcpyDeviceToHost, h->stream));
+        return sync(h);
+    }();
+    free_pool(tmp);
+    return rc;
 }
 
 // ---- batch of independent calibrations (calib_batch.cuh) -------------------------------------------

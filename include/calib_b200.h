@@ -154,6 +154,17 @@ int calib_time_kernel(calib_t* h, const double* P, double lam, int which, int re
 int calib_measure_fp64_peak(int device_id, double* tflops);
 int calib_flush_l2(calib_t* h);
 
+/* Calibrator._refineHomographies / _refineHomography, src/calibrate.py:60-115 (the step before the
+ * refinement in estimateCalibrationParameters, :53): M independent Levenberg-Marquardt fits of the 9
+ * homography entries to the handle's detections (model X, Y -> sensor u, v), HomographyJacobian
+ * (src/jacobian.py:88-121) in analytic form, one warp per view, the whole loop in one launch.
+ * H_inout: M x 9 row-major (h11 h12 h13 h21 ... h33) initial homographies, replaced by the refined
+ * ones divided by h33 (:108-109).  The reference hard-codes maxIters = 20 and lambda0 = 1e-3 (:77-78)
+ * and uses the class constants for the rest.  iters_out (nullable): M; trace (nullable): M x maxIters
+ * x 4 rows (E, E', lambda, accepted), zero after a view's last iteration. */
+int calib_refine_homographies(calib_t* h, double* H_inout, int maxIters, double lam0, double lam_min,
+                              double lam_max, double err_min, int* iters_out, double* trace);
+
 /* Multi-GPU, one process per GPU: views are sharded, every rank holds the L shared parameters
  * and its own views' extrinsics.  The reduced system (L x L Schur complement, its right-hand
  * side and the cost) is all-reduced over NCCL each iteration; everything else is local.

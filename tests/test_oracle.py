@@ -129,3 +129,34 @@ def test_reference_quirks():
     P2 = np.concatenate([P, [170, 5, 3, 0.1, 0.2, 1.1]])
     J = onp.dense_jacobian(0, P2, np.array([0, 2, 4]), np.vstack([pts, pts]))
     assert J.shape == (8, 22) and J[0, 0] != 0 and J[-1, -1] != 0 and J[0, 16] == 0
+
+
+# ---- per-view homography refinement --------------------------------
+def _hom_cases():
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "homography.npz"))
+    return g
+
+
+@pytest.mark.parametrize("case", ["cfg1", "cfg1n", "cfg2", "itest"])
+def test_homography_oracle_vs_reference(golden, case):
+    """The numpy restatement of Calibrator._refineHomography / HomographyJacobian against the
+    reference's own outputs (oracle/make_golden_homography.py): Jacobian entries <= 1e-12 relative,
+    identical accept/reject and costs up to the cost plateau, refined homography <= 1e-6 relative
+    (after the plateau both sides take rounding-level steps along a flat valley)."""
+    import calib_oracle as onp
+    hg = _hom_cases()
+    g = golden(case)
+    offs, mp, sp = g["view_offsets"], g["model_pts"], g["sensor_pts"]
+    J = onp.homography_jacobian(hg[case + "_H0"][0], mp[offs[0]:offs[1]])
+    assert np.abs(J - hg[case + "_J0"]).max() <= 1e-12 * np.abs(hg[case + "_J0"]).max()
+    for v in range(len(offs) - 1):
+        H, it, tr = onp.homography_lm(hg[case + "_H0"][v], sp[offs[v]:offs[v + 1]], mp[offs[v]:offs[v + 1]])
+        gt = hg[case + "_trace"][v][:int(hg[case + "_iters"][v])]
+        pl = np.where(np.abs(gt[:, 1] - gt[:, 0]) <= 1e-10 * gt[:, 0])[0]
+        stop = min(len(gt), len(tr), int(pl[0]) if len(pl) else 99)
+        assert stop >= 2
+        assert np.array_equal(gt[:stop, 3], tr[:stop, 3]) and np.array_equal(gt[:stop, 2], tr[:stop, 2])
+        assert np.allclose(gt[:stop, :2], tr[:stop, :2], rtol=1e-9)
+        ref = hg[case + "_Href"][v]
+        assert (np.abs(H.ravel() - ref) / np.maximum(np.abs(ref), 1e-3)).max() < 1e-6

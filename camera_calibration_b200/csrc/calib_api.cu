@@ -57,6 +57,7 @@ struct calib_handle {
     int model = 0, L = 0, device = 0, n_sm = 148;
     int64_t M = 0, N = 0, K = 0;
     std::vector<int64_t> view_offsets;
+    std::vector<char> meta_host;           // staging of the partition tables (build_tasks)
     int seg = 0;
     Dev dev{};
     cudaStream_t stream = nullptr;
@@ -255,7 +256,7 @@ static void cut_points(const std::vector<int64_t>& offs, int64_t M, int64_t N, i
 
 // (Re)builds the partition of the points and everything sized by it.  seg = points per warp
 // (0 = automatic: one chunk per resident warp of the persistent grids).
-static int build_tasks(calib_handle* h, int seg) {
+static int build_tasks(calib_handle* h, int seg, bool sync_now = true) {
     drop_graph(h);
     if (h->arena_part) { cudaFreeAsync(h->arena_part, h->stream); h->arena_part = nullptr; }
     h->seg = seg;
@@ -307,14 +308,15 @@ static int build_tasks(calib_handle* h, int seg) {
     CUDA_TRY(h, cudaMallocAsync(&h->arena_part, a.bytes, h->stream));
     a.base = (char*)h->arena_part;
     // one upload for the five index tables
-    std::vector<char> meta(meta_bytes, 0);
+    std::vector<char>& meta = h->meta_host;      // stays alive until the stream has been synchronised
+    meta.assign(meta_bytes, 0);
     memcpy(meta.data() + o_evp, evp.data(), evp.size() * sizeof(Piece));
     memcpy(meta.data() + o_evc, evr.data(), evr.size() * sizeof(WarpRec));
     memcpy(meta.data() + o_vp, vp.data(), vp.size() * sizeof(int));
     memcpy(meta.data() + o_cop, cop.data(), cop.size() * sizeof(Piece));
     memcpy(meta.data() + o_coc, cor.data(), cor.size() * sizeof(WarpRec));
     CUDA_TRY(h, cudaMemcpyAsync(a.base, meta.data(), meta_bytes, cudaMemcpyHostToDevice, h->stream));
-    CUDA_TRY(h, cudaStreamSynchronize(h->stream));   // meta is a local
+    if (sync_now) CUDA_TRY(h, cudaStreamSynchronize(h->stream));
     d.ev_piece = a.at<Piece>(o_evp); d.ev_rec = a.at<WarpRec>(o_evc); d.view_piece = a.at<int>(o_vp);
     d.co_piece = a.at<Piece>(o_cop); d.co_rec = a.at<WarpRec>(o_coc);
     d.partA = a.at<double>(o_pA); d.partE = a.at<double>(o_pE); d.partBD = a.at<double>(o_pBD);
@@ -333,6 +335,8 @@ static int ensure_trace(calib_handle* h, int iters) {
     h->trace_cap = iters;
     return CALIB_OK;
 }
+
+namespace { int build_loop_graph(calib_handle* h); }
 
 extern "C" const char* calib_last_error(const calib_t* h) {
     return h ? h->err.c_str() : g_last_error.c_str();
@@ -419,8 +423,15 @@ extern "C" int calib_create(calib_t** out, int model, int64_t M, const int64_t* 
         }
     }
 #undef TRY_
-    int rc = build_tasks(h, 0);     // synchronises the stream: the caller's buffers are free again
+    int rc = build_tasks(h, 0, false);
     if (rc) { g_last_error = h->err; return bail(rc); }
+    // the default loop graph is built here, on the host, while the detections are still crossing PCIe
+    // (a setting that changes the iteration drops it and lm_run rebuilds it)
+    if (build_loop_graph(h) != CALIB_OK) { cudaGetLastError(); drop_graph(h); }
+    {   // the caller's buffers are free again once the stream is idle
+        cudaError_t e = cudaStreamSynchronize(h->stream);
+        if (e != cudaSuccess) { h->err = cudaGetErrorString(e); g_last_error = h->err; return bail(CALIB_E_CUDA); }
+    }
     *out = h;
     return CALIB_OK;
 }
@@ -462,8 +473,8 @@ extern "C" int calib_set_loop_mode(calib_t* h, int mode) {
 
 extern "C" int calib_set_pdl(calib_t* h, int on) {
     if (!h) return fail(nullptr, CALIB_E_ARG, "NULL handle");
+    if (h->pdl != (on ? 1 : 0)) drop_graph(h);
     h->pdl = on ? 1 : 0;
-    drop_graph(h);
     return CALIB_OK;
 }
 
@@ -478,8 +489,8 @@ extern "C" int calib_set_ladder(calib_t* h, int max_candidates) {
 extern "C" int calib_set_cost_staging(calib_t* h, int mode) {
     if (!h) return fail(nullptr, CALIB_E_ARG, "NULL handle");
     if (mode < -1 || mode > 1) return fail(h, CALIB_E_ARG, "calib_set_cost_staging: -1 auto, 0 loads, 1 bulk copies");
+    if (h->cost_tma != mode) drop_graph(h);
     h->cost_tma = mode;
-    drop_graph(h);
     return CALIB_OK;
 }
 

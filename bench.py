@@ -181,6 +181,16 @@ def run_reference_arm(args):
     print(json.dumps(line), flush=True)
 
 
+def ncu_traffic(workload, n_points):
+    """DRAM bytes per launch of k_eval from the committed ncu capture (profiles/ncu_traffic.json), or
+    None when there is no capture of this workload at this size."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))[workload]
+        return int(t["k_eval"]) if int(t["points"]) == int(n_points) else None
+    except Exception:
+        return None
+
+
 def pinned_copy(L, arr):
     """numpy view of a page-locked copy of arr (calib_host_alloc); returns (view, ptr)."""
     ptr = L.calib_host_alloc(max(arr.nbytes, 8))
@@ -513,7 +523,7 @@ def main():
             os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         roof = {"bound": "fp64", "kernel": "k_eval", "achieved": fl / avg_s / 1e12, "peak": peak64,
-                "unit": "TFLOP/s", "frac": fl / avg_s / 1e12 / peak64, "traffic": None,
+                "unit": "TFLOP/s", "frac": fl / avg_s / 1e12 / peak64, "traffic": ncu_traffic(args.workload, n_loc),
                 "peak_source": "DFMA micro-benchmark in this run (calib_measure_fp64_peak): FP64 is not in "
                                "MEASURED_PEAKS.json and the kernel is FP64-pipe bound, not HBM bound",
                 "flops_per_point": FLOPS_PER_POINT[model], "points_per_launch": n_loc,

@@ -430,18 +430,38 @@ class Calibrator:
 
     # -- entry points -----------------------------------------------------------------------
     def calibrate(self, allDetections, maxIters, initial=None):
-        """src/calibrate.py:21-39.  The closed-form initial estimate is outside the GPU path
-        (SURVEY.md section 8f); pass initial=(A, W, k) or subclass estimateCalibrationParameters."""
-        if initial is None:
-            initial = self.estimateCalibrationParameters(allDetections)
-        Ainitial, Winitial, kInitial = initial
-        return self.refineCalibrationParameters(Ainitial, Winitial, kInitial, allDetections,
-                                                maxIters, shouldPrint=True)
+        """src/calibrate.py:21-39.  The detections are uploaded once; the initial estimate
+        (estimateCalibrationParameters) and the refinement run on the same device handle.
+        initial=(A, W, k) skips the closed-form estimate."""
+        n_points = sum(len(m) for s, m in allDetections)
+        offs, mp, sp = flatten_detections(allDetections, out=self._pinned.reserve(n_points))
+        prob = Problem(self._model, offs, mp, sp, self._device)
+        try:
+            if initial is None:
+                initial = self._estimate_on(prob)
+            Ainitial, Winitial, kInitial = initial
+            return self._refine_on(prob, Ainitial, Winitial, kInitial, maxIters, True)
+        finally:
+            prob.close()
 
     def estimateCalibrationParameters(self, allDetections):
-        raise NotImplementedError(
-            "the linear initial estimate (src/calibrate.py:41-58) is not part of the GPU path; "
-            "use the reference's Calibrator.estimateCalibrationParameters and pass its result")
+        """src/calibrate.py:41-58: DLT homographies -> per-view LM refinement -> intrinsics ->
+        extrinsics -> linear distortion estimate.  Returns (Ainitial, Winitial, kInitial)."""
+        prob = Problem.from_detections(self._model, allDetections, self._device)
+        try:
+            return self._estimate_on(prob)
+        finally:
+            prob.close()
+
+    def _estimate_on(self, prob):
+        from . import linearcalibrate
+        Hs = linearcalibrate.estimateHomographies(prob)
+        Hsref, iters, _ = prob.refine_homographies(Hs, 20, 1e-3, self._λmin, self._λmax, self._Pt_error_min)
+        self.lastHomographyIters = iters
+        Ainitial = linearcalibrate.computeIntrinsicMatrix(Hsref)
+        Winitial = linearcalibrate.computeExtrinsics(Hsref, Ainitial)
+        kInitial = linearcalibrate.estimateDistortion(prob, Ainitial, Winitial)
+        return Ainitial, Winitial, kInitial
 
     def _refineHomographies(self, Hs, allDetections):
         """src/calibrate.py:60-68: per-view LM refinement of the DLT homographies, all views in one
@@ -466,17 +486,23 @@ class Calibrator:
             # the reference returns an unbound Pt_error (src/calibrate.py:171)
             raise UnboundLocalError("cannot access local variable 'Pt_error' where it is not "
                                     "associated with a value")
-        ts = time.time()
-        Pt = self._composeParameterVector(Ainitial, Winitial, kInitial)
         n_points = sum(len(m) for s, m in allDetections)
         offs, mp, sp = flatten_detections(allDetections, out=self._pinned.reserve(n_points))
         prob = Problem(self._model, offs, mp, sp, self._device)
         try:
-            sse, P, iters, trace = prob.lm_run(Pt, int(maxIters), self._λinitial, self._λmin,
-                                               self._λmax, self._Pt_error_min)
-            self.lastDeviceMs = prob.last_run_stats()[0]
+            return self._refine_on(prob, Ainitial, Winitial, kInitial, maxIters, shouldPrint)
         finally:
             prob.close()
+
+    def _refine_on(self, prob, Ainitial, Winitial, kInitial, maxIters, shouldPrint):
+        if int(maxIters) <= 0:
+            raise UnboundLocalError("cannot access local variable 'Pt_error' where it is not "
+                                    "associated with a value")
+        ts = time.time()
+        Pt = self._composeParameterVector(Ainitial, Winitial, kInitial)
+        sse, P, iters, trace = prob.lm_run(Pt, int(maxIters), self._λinitial, self._λmin,
+                                           self._λmax, self._Pt_error_min)
+        self.lastDeviceMs = prob.last_run_stats()[0]
         self.lastTrace, self.lastIters = trace, iters
         if shouldPrint:
             for it, (E, E1, lam, acc) in enumerate(trace):

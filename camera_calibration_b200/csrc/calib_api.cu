@@ -18,6 +18,7 @@
 #include "calib_solve.cuh"
 #include "calib_batch.cuh"
 #include "calib_homography.cuh"
+#include "calib_linear.cuh"
 
 using namespace calib;
 
@@ -1241,6 +1242,58 @@ extern "C" int calib_refine_homographies(calib_t* h, double* H_inout, int maxIte
     return rc;
 }
 
+// ---- per-point parts of the closed-form initial estimate (calib_linear.cuh) ---------------------------
+namespace {
+int linear_call(calib_handle* h, int which, const double* A9, const double* W12, double* out0, size_t n0,
+                double* out1, size_t n1) {
+    const size_t M = (size_t)h->M;
+    std::vector<void*> tmp;
+    int rc = [&]() -> int {
+        long long* d_offs = nullptr;
+        double *d0 = nullptr, *d1 = nullptr, *dA = nullptr, *dW = nullptr;
+        CUDA_TRY(h, dalloc(tmp, &d_offs, M + 1));
+        CUDA_TRY(h, dalloc(tmp, &d0, M * n0));
+        if (n1) CUDA_TRY(h, dalloc(tmp, &d1, M * n1));
+        CUDA_TRY(h, cudaMemcpyAsync(d_offs, h->view_offsets.data(), (M + 1) * 8, cudaMemcpyHostToDevice, h->stream));
+        LinDev d;
+        memset(&d, 0, sizeof d);
+        d.X = h->dev.X; d.Y = h->dev.Y; d.Z = h->dev.Z; d.U = h->dev.U; d.V = h->dev.V;
+        d.offs = d_offs; d.M = (int)M; d.model = h->model;
+        const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>(((int64_t)M + kBlockWarps - 1) / kBlockWarps, 8 * h->n_sm));
+        if (which == 0) {
+            d.gram = d0; d.norm = d1;
+            k_dlt_gram<<<blocks, kBlockThreads, 0, h->stream>>>(d);
+        } else {
+            CUDA_TRY(h, dalloc(tmp, &dA, 9));
+            CUDA_TRY(h, dalloc(tmp, &dW, M * 12));
+            CUDA_TRY(h, cudaMemcpyAsync(dA, A9, 72, cudaMemcpyHostToDevice, h->stream));
+            CUDA_TRY(h, cudaMemcpyAsync(dW, W12, M * 96, cudaMemcpyHostToDevice, h->stream));
+            d.A = dA; d.W = dW; d.drows = d0;
+            if (h->model == 0) k_distortion_rows<0><<<blocks, kBlockThreads, 0, h->stream>>>(d);
+            else k_distortion_rows<1><<<blocks, kBlockThreads, 0, h->stream>>>(d);
+        }
+        CUDA_TRY(h, cudaGetLastError());
+        CUDA_TRY(h, cudaMemcpyAsync(out0, d0, M * n0 * 8, cudaMemcpyDeviceToHost, h->stream));
+        if (n1) CUDA_TRY(h, cudaMemcpyAsync(out1, d1, M * n1 * 8, cudaMemcpyDeviceToHost, h->stream));
+        return sync(h);
+    }();
+    free_pool(tmp);
+    return rc;
+}
+}  // namespace
+
+extern "C" int calib_dlt_gram(calib_t* h, double* gram, double* norm) {
+    RC(check_handle(h));
+    if (!gram || !norm) return fail(h, CALIB_E_ARG, "calib_dlt_gram: NULL output");
+    return linear_call(h, 0, nullptr, nullptr, gram, kGramN, norm, kNormN);
+}
+
+extern "C" int calib_distortion_rows(calib_t* h, const double* A, const double* W, double* rows) {
+    RC(check_handle(h));
+    if (!A || !W || !rows) return fail(h, CALIB_E_ARG, "calib_distortion_rows: NULL argument");
+    return linear_call(h, 1, A, W, rows, kDistN, nullptr, 0);
+}
+
 // ---- batch of independent calibrations (calib_batch.cuh) -------------------------------------------
 struct calib_batch_handle {
     int model = 0, L = 0, device = 0;
@@ -1417,6 +1470,10 @@ extern "C" int calib_batch_lm_run(calib_batch_t* h, double* P_inout, int maxIter
 // latency-study builds only (not in the header): one pass at P, then the globaltimer stamps
 extern "C" int calib_debug_stamps(calib_t* h, const double* P, double lam, unsigned long long* out) {
     RC(check_handle(h));
+    if (!P) {      // just read what the last run left (the stamps of its last pass)
+        CUDA_TRY(h, cudaMemcpy(out, h->dev.stamps, (size_t)4 * kStampBlocks * 8 * 8, cudaMemcpyDeviceToHost));
+        return CALIB_OK;
+    }
     h->cur = 0;
     h->dev.use_cond = 0;
     RC(upload_to(h, P, 0));

@@ -48,7 +48,6 @@ __global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
     __shared__ __align__(16) ViewC sview[kBlockWarps][1];
     __shared__ double sred[kBlockWarps][kNA];
     __shared__ double sE[kBlockWarps];
-    __shared__ int s_last;
     const int cur = st->cur;
     const double* P = d.Pbuf + (long long)cur * d.K;
     const ViewC* const views[1] = {d.views + (long long)cur * d.M};
@@ -109,52 +108,6 @@ __global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
 #pragma unroll
         for (int k = 1; k < kBlockWarps; ++k) s = __dadd_rn(s, sE[k]);
         d.partE[blockIdx.x] = s;
-    }
-    // The last block to finish sums the block rows (fixed order) into redA: the intrinsic block and
-    // the cost do not change while steps from this point are rejected, so this is paid once per
-    // evaluation and k_schur reads 65 numbers instead of 148 rows on every pass.
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        const unsigned int prev = atomicAdd(&d.st->cnt_eval, 1u);
-        s_last = (prev == gridDim.x - 1);
-    }
-    __syncthreads();
-    if (!s_last) return;
-    __threadfence();
-    {
-        constexpr int R = 19;                       // rows per warp held in flight (148 blocks / 8 warps)
-        double a0 = 0.0, a1 = 0.0, e = 0.0;
-        for (int r0 = warp; r0 < d.ev_blocks; r0 += kBlockWarps * R) {
-            double t0[R], t1[R];
-#pragma unroll
-            for (int k = 0; k < R; ++k) {
-                const int r = r0 + k * kBlockWarps;
-                const double* row = d.partA + (long long)r * kNA;
-                t0[k] = r < d.ev_blocks ? __ldcg(row + lane) : 0.0;
-                t1[k] = r < d.ev_blocks ? __ldcg(row + lane + 32) : 0.0;
-            }
-#pragma unroll
-            for (int k = 0; k < R; ++k) { a0 += t0[k]; a1 += t1[k]; }
-        }
-        for (int r = threadIdx.x; r < d.ev_blocks; r += kBlockThreads) e = __dadd_rn(e, __ldcg(d.partE + r));
-        e = warp_sum(e);
-        sred[warp][lane] = a0; sred[warp][lane + 32] = a1;
-        if (lane == 0) sE[warp] = e;
-    }
-    __syncthreads();
-    if (threadIdx.x < kNA) {
-        double s = sred[0][threadIdx.x];
-#pragma unroll
-        for (int k = 1; k < kBlockWarps; ++k) s += sred[k][threadIdx.x];
-        d.redA[kRedA + threadIdx.x] = s;
-    } else if (threadIdx.x == kNA) {
-        double s = sE[0];
-#pragma unroll
-        for (int k = 1; k < kBlockWarps; ++k) s = __dadd_rn(s, sE[k]);
-        d.redA[kRedE] = s;
-        d.st->cnt_eval = 0;
-        d.st->n_eval += 1;
     }
     STAMP(d, 0, 4);
 }

@@ -213,6 +213,7 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
     __shared__ double sv[kBlockWarps][kNBD];       // the view's summed piece rows; reused for sums
     __shared__ double sz[kBlockWarps][NZ * 6];     // Z = L^-1 [B^T | g_v], column-major by c
     __shared__ double sl[kBlockWarps][24];         // packed lower factor of the view block
+    __shared__ double sga[kBlockWarps][kNA], sge[kBlockWarps];
     __shared__ double sred[kRedN];                 // the reduced system in the layout of red[]
     __shared__ double sdense[kJMax * (L * L + L)];  // its dense form, per candidate
     __shared__ int s_last;
@@ -322,8 +323,48 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
     STAMP(d, 1, 3);
     if (!s_last) return;
     __threadfence();
-    // the intrinsic block, g_c and the cost at the current point, as k_eval's last block left them
-    if (tid < kRedW0) sred[tid] = tid <= kRedE ? __ldcg(d.redA + tid) : 0.0;
+    // The intrinsic block, g_c and the cost at the current point: after an evaluation the block rows
+    // k_eval wrote are summed here (fixed order, all loads of a warp in flight at once) and kept in
+    // redA; while steps from this point are rejected they do not change and 65 numbers are read back.
+    if (st->need_eval) {
+        constexpr int R = 19;                       // rows per warp held in flight (148 blocks / 8 warps)
+        double a0 = 0.0, a1 = 0.0, e = 0.0;
+        for (int r0 = warp; r0 < d.ev_blocks; r0 += kBlockWarps * R) {
+            double t0[R], t1[R];
+#pragma unroll
+            for (int k = 0; k < R; ++k) {
+                const int r = r0 + k * kBlockWarps;
+                const double* row = d.partA + (long long)r * kNA;
+                t0[k] = r < d.ev_blocks ? __ldcg(row + lane) : 0.0;
+                t1[k] = r < d.ev_blocks ? __ldcg(row + lane + 32) : 0.0;
+            }
+#pragma unroll
+            for (int k = 0; k < R; ++k) { a0 += t0[k]; a1 += t1[k]; }
+        }
+        for (int r = tid; r < d.ev_blocks; r += kBlockThreads) e = __dadd_rn(e, __ldcg(d.partE + r));
+        e = warp_sum(e);
+        sga[warp][lane] = a0; sga[warp][lane + 32] = a1;
+        if (lane == 0) sge[warp] = e;
+        __syncthreads();
+        if (tid < kNA) {
+            double s = sga[0][tid];
+#pragma unroll
+            for (int k = 1; k < kBlockWarps; ++k) s += sga[k][tid];
+            sred[kRedA + tid] = s;
+            d.redA[kRedA + tid] = s;
+        } else if (tid == kNA) {
+            double s = sge[0];
+#pragma unroll
+            for (int k = 1; k < kBlockWarps; ++k) s = __dadd_rn(s, sge[k]);
+            sred[kRedE] = s;
+            d.redA[kRedE] = s;
+            st->n_eval += 1;
+        } else if (tid < kRedW0) {
+            sred[tid] = 0.0;
+        }
+    } else if (tid < kRedW0) {
+        sred[tid] = tid <= kRedE ? __ldcg(d.redA + tid) : 0.0;
+    }
     if (tid == 0) st->cnt_schur = 0;
     STAMP(d, 1, 4);
     for (int j = 0; j < J; ++j) {

@@ -165,6 +165,24 @@ int calib_flush_l2(calib_t* h);
 int calib_refine_homographies(calib_t* h, double* H_inout, int maxIters, double lam0, double lam_min,
                               double lam_max, double err_min, int* iters_out, double* trace);
 
+/* Per-point parts of the closed-form initial estimate, Calibrator.estimateCalibrationParameters
+ * (src/calibrate.py:41-58), on the handle's detections; what is left for the caller is O(M) small
+ * dense algebra (see camera_calibration_b200/linearcalibrate.py and INTEGRATION.md).
+ *
+ * calib_dlt_gram: linearcalibrate.estimateHomography, src/linearcalibrate.py:24-58.  Per view the point
+ * normalisations of computeNormalizationMatrix (:61-91) -- norm: M x 6 = (mean_u, mean_v, scale_a,
+ * mean_X, mean_Y, scale_b) -- and the Gram matrix M^T M of the 2N x 9 DLT matrix of :46-52 in packed
+ * form -- gram: M x 24 = the six entries (XX, XY, X, YY, Y, 1) of p p^T, p = (X, Y, 1) normalised,
+ * summed with weights 1, u, v, u^2 + v^2: M^T M = [[P1, 0, -Pu], [0, P1, -Pv], [-Pu, -Pv, Pq]].  The
+ * homography is its eigenvector of the smallest eigenvalue, de-normalised (:55-57).
+ *
+ * calib_distortion_rows: DistortionModel.estimateDistortion, src/distortion.py:110-191 (radial-
+ * tangential) / :222-271 (fisheye).  A: 3 x 3 intrinsic matrix, W: M x 12 board poses in the camera
+ * (R row-major, then t).  rows: M x 20 per-view sums: the upper triangle of D^T D (nd (nd+1) / 2,
+ * row-major) then D^T Ddot (nd), nd = 5 | 4, zero padded; k solves (sum D^T D) k = sum D^T Ddot. */
+int calib_dlt_gram(calib_t* h, double* gram, double* norm);
+int calib_distortion_rows(calib_t* h, const double* A, const double* W, double* rows);
+
 /* Multi-GPU, one process per GPU: views are sharded, every rank holds the L shared parameters
  * and its own views' extrinsics.  The reduced system (L x L Schur complement, its right-hand
  * side and the cost) is all-reduced over NCCL each iteration; everything else is local.

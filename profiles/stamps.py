@@ -27,25 +27,40 @@ fn = L.calib_debug_stamps
 fn.restype = ctypes.c_int
 fn.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_double), ctypes.c_double, ctypes.c_void_p]
 P = np.ascontiguousarray(P0, dtype=np.float64)
+
+
+def report(title):
+    t = out.astype(np.float64)
+    t[t == 0] = np.nan
+    t0 = np.nanmin(t[1:]) if np.isnan(t[0]).all() else np.nanmin(t)
+    t = (t - t0) * 1e-3   # us since the first stamp of the pass
+    names = ["k_eval", "k_schur", "k_backsub", "k_cost"]
+    slots = {0: ["entry", "sweep1 done", "sweep2 done", "after block barrier", "end"],
+             1: ["entry", "view rows loaded (last view)", "view phase done", "ticket taken", "last: A gathered",
+                 "last: red written", "last: solved"],
+             2: ["entry", "end"],
+             3: ["entry", "sweep done", "ticket taken", "last: end"]}
+    print(f"{title}: M={len(offs) - 1} N={offs[-1]}   (us since the first stamp; min / median / max over blocks)")
+    for k in range(4):
+        print(names[k])
+        for s_, label in enumerate(slots[k]):
+            col = t[k, :, s_]
+            col = col[~np.isnan(col)]
+            if len(col) == 0:
+                continue
+            print(f"   {label:34s} n={len(col):5d}  {col.min():8.2f} {np.median(col):8.2f} {col.max():8.2f}")
+
+
 rc = fn(prob._h, P.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), 1e-3, out.ctypes.data_as(ctypes.c_void_p))
 assert rc == 0
-t = out.astype(np.float64)
-t[t == 0] = np.nan
-t0 = np.nanmin(t)
-t = (t - t0) * 1e-3   # us since the first stamp of the pass
-names = ["k_eval", "k_schur", "k_backsub", "k_cost"]
-slots = {0: ["entry", "sweep1 done", "sweep2 done", "after block barrier", "end"],
-         1: ["entry", "view rows loaded (last view)", "view phase done", "ticket taken", "last: A gathered",
-             "last: red written", "last: solved"],
-         2: ["entry", "end"],
-         3: ["entry", "sweep done", "ticket taken", "last: end"]}
-print(f"{name} x{scale}: M={len(offs) - 1} N={offs[-1]}   (us since the first stamp; min / median / max over blocks)")
-for k in range(4):
-    print(names[k])
-    for s, label in enumerate(slots[k]):
-        col = t[k, :, s]
-        col = col[~np.isnan(col)]
-        if len(col) == 0:
-            continue
-        print(f"   {label:34s} n={len(col):5d}  {col.min():8.2f} {np.median(col):8.2f} {col.max():8.2f}")
+report(f"{name} x{scale}, one pass, plain stream launches, J = 1")
+# the last pass of a whole refinement inside the WHILE graph (rejected steps: no evaluation, J = 4):
+# stamps of earlier passes are overwritten, k_eval's are from the last evaluation (ignore them)
+for mode, label in ((2, "WHILE graph"), (1, "host-driven iteration graphs")):
+    prob.set_loop_mode(mode)
+    sse, Pr, iters, tr = prob.lm_run(P0, 100)
+    rc = fn(prob._h, None, 0.0, out.ctypes.data_as(ctypes.c_void_p))
+    assert rc == 0
+    out[0] = 0
+    report(f"{name} x{scale}, last pass of a {iters}-iteration run, {label}")
 prob.close()

@@ -455,3 +455,48 @@ def test_homography_mirror_and_edge_cases(golden):
     dets2 = [dets[0], (dets[1][0][:3], dets[1][1][:3]), (dets[2][0][:0], dets[2][1][:0]), dets[3]]
     out2 = cal._refineHomographies(Hs[:4], dets2)
     assert np.array_equal(out2[0], out[0]) and np.array_equal(out2[3], out[3])
+
+
+# ---- closed-form initial estimate ----------------------------------
+@pytest.mark.parametrize("case", ["cfg1", "cfg1n", "cfg2", "itest"])
+def test_initial_estimate_vs_reference(golden, case):
+    """Calibrator.estimateCalibrationParameters (DLT Gram matrices, homography LM and distortion rows
+    on the device, O(M) algebra on the host) against the reference's own P0 and against the oracle.
+    Tolerances: DLT homographies <= 1e-7 relative to the reference's (eigenvector of M^T M instead of
+    the singular vector of M), P0 <= 5e-6 relative (dominated by the rounding-level plateau steps of the
+    homography refinement on both sides; angles compared modulo 360 degrees)."""
+    import os
+    import linear_oracle as lo
+    from camera_calibration_b200 import linearcalibrate
+    hg = np.load(os.path.join(os.path.dirname(__file__), "golden", "homography.npz"))
+    g = golden(case)
+    offs, mp, sp, model = g["view_offsets"], g["model_pts"], g["sensor_pts"], int(g["model"])
+    dets = [(sp[offs[v]:offs[v + 1]], mp[offs[v]:offs[v + 1]]) for v in range(len(offs) - 1)]
+    prob = _problem(g)
+    H0 = linearcalibrate.estimateHomographies(prob).reshape(-1, 9)
+    ref = hg[case + "_H0"]
+    assert (np.abs(H0 - ref) / np.maximum(np.abs(ref), 1e-3)).max() < 1e-7
+    # distortion rows against the oracle at the oracle's own (A, W)
+    A, Ws, k, Hs = lo.estimate_calibration_parameters(model, dets)
+    kd = linearcalibrate.estimateDistortion(prob, A, Ws)
+    assert np.allclose(kd, k, rtol=1e-6, atol=1e-9)
+    prob.close()
+    cal = cc.Calibrator("radtan" if model == 0 else "fisheye")
+    A0, W0, k0 = cal.estimateCalibrationParameters(dets)
+    P = cal._composeParameterVector(A0, W0, k0).ravel()
+    d = np.abs(P - g["P0"])
+    d = np.minimum(d, np.abs(d - 360))
+    assert (d / np.maximum(np.abs(g["P0"]), 1e-3)).max() < 5e-6
+
+
+def test_calibrate_end_to_end_like_itest(golden):
+    """The reference's own acceptance test (tests/itest_main.py:12-29) on our Calibrator.calibrate:
+    noise-free synthetic data -> intrinsics and distortion within 1e-9 of the ground truth, sse ~ 0."""
+    c = synth.config("cfg1")
+    cal = cc.Calibrator("radtan")
+    import contextlib
+    import io
+    with contextlib.redirect_stdout(io.StringIO()):
+        sse, A, W, k = cal.calibrate(c["dets"], 100)
+    assert sse < 1e-10
+    assert np.allclose(A, c["A"], atol=1e-9) and np.allclose(k, c["k"], atol=1e-9)

@@ -160,3 +160,25 @@ def test_homography_oracle_vs_reference(golden, case):
         assert np.allclose(gt[:stop, :2], tr[:stop, :2], rtol=1e-9)
         ref = hg[case + "_Href"][v]
         assert (np.abs(H.ravel() - ref) / np.maximum(np.abs(ref), 1e-3)).max() < 1e-6
+
+
+# ---- closed-form initial estimate ----------------------------------
+@pytest.mark.parametrize("case", ["cfg1", "cfg1n", "cfg2", "itest"])
+def test_linear_oracle_vs_reference(golden, case):
+    """oracle/linear_oracle.py against the reference: its DLT homographies are the reference's bit for
+    bit (same normalisation, same SVD), and the whole estimateCalibrationParameters chain reproduces the
+    reference's P0 (what its own linear stage handed to the LM) to <= 2e-6 relative -- the limit is the
+    homography refinement's rounding-level plateau steps (see test_homography_oracle_vs_reference)."""
+    import linear_oracle as lo
+    import camera_calibration_b200 as cc
+    hg = _hom_cases()
+    g = golden(case)
+    offs, mp, sp, model = g["view_offsets"], g["model_pts"], g["sensor_pts"], int(g["model"])
+    dets = [(sp[offs[v]:offs[v + 1]], mp[offs[v]:offs[v + 1]]) for v in range(len(offs) - 1)]
+    H0 = np.array([lo.estimate_homography(s[:, :2], m[:, :2]).ravel() for s, m in dets])
+    assert np.abs(H0 - hg[case + "_H0"]).max() <= 1e-12 * np.abs(hg[case + "_H0"]).max()
+    A, Ws, k, Hs = lo.estimate_calibration_parameters(model, dets)
+    P = cc.Calibrator("radtan" if model == 0 else "fisheye")._composeParameterVector(A, Ws, k).ravel()
+    d = np.abs(P - g["P0"])
+    d = np.minimum(d, np.abs(d - 360))
+    assert (d / np.maximum(np.abs(g["P0"]), 1e-3)).max() < 2e-6

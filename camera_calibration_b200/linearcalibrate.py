@@ -70,7 +70,7 @@ def computeIntrinsicMatrix(Hs):
     V = np.empty((2 * len(H), 6))
     V[0::2] = _vec(H, 0, 1)
     V[1::2] = _vec(H, 0, 0) - _vec(H, 1, 1)
-    b = np.linalg.svd(V)[2][-1]
+    b = np.linalg.svd(V, full_matrices=False)[2][-1]      # 2M >= 6: the same V^T as the full SVD
     sign = -1.0 if (b[0] < 0 or b[2] < 0 or b[5] < 0) else 1.0
     B = sign * np.array([[b[0], b[1], b[3]], [b[1], b[2], b[4]], [b[3], b[4], b[5]]])
     A = np.linalg.inv(np.linalg.cholesky(B).T)

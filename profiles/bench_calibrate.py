@@ -1,0 +1,79 @@
+"""Whole Calibrator.calibrate() (closed-form initial estimate + LM refinement, src/calibrate.py:21-39) at
+a large configuration, stage by stage, against the vectorised numpy oracle of the linear stage.  The
+reference itself cannot run this size (np.vstack per point in estimateHomography / estimateDistortion).
+usage: python profiles/bench_calibrate.py [cfg3] [scale] [cpu_views]"""
+import contextlib
+import io
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+import camera_calibration_b200 as cc  # noqa: E402
+from camera_calibration_b200 import linearcalibrate, synth  # noqa: E402
+import linear_oracle as lo  # noqa: E402
+
+name = sys.argv[1] if len(sys.argv) > 1 else "cfg3"
+scale = float(sys.argv[2]) if len(sys.argv) > 2 else 1.0
+cpu_views = int(sys.argv[3]) if len(sys.argv) > 3 else 50
+c = synth.config(name, scale)
+dets = c["dets"]
+M = len(dets)
+cal = cc.Calibrator(c["model"])
+offs, mp, sp = cc.flatten_detections(dets)
+
+
+def stages():
+    t = {}
+    t0 = time.perf_counter()
+    prob = cc.Problem(c["model"], offs, mp, sp)
+    t["upload"] = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    Hs = linearcalibrate.estimateHomographies(prob)
+    t["dlt"] = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    Hr, iters, _ = prob.refine_homographies(Hs, 20)
+    t["homography_lm"] = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    A = linearcalibrate.computeIntrinsicMatrix(Hr)
+    W = linearcalibrate.computeExtrinsics(Hr, A)
+    t["intrinsics_extrinsics_host"] = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    k = linearcalibrate.estimateDistortion(prob, A, W)
+    t["distortion"] = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    P0 = cal._composeParameterVector(A, W, k).ravel()
+    sse, P, it, tr = prob.lm_run(P0, 100)
+    t["refinement"] = time.perf_counter() - t0
+    prob.close()
+    return t, (A, k, sse, it)
+
+
+for _ in range(2):
+    stages()
+best = None
+for _ in range(5):
+    t, res = stages()
+    if best is None or sum(t.values()) < sum(best.values()):
+        best = t
+A, k, sse, it = res
+t0 = time.perf_counter()
+with contextlib.redirect_stdout(io.StringIO()):
+    out = cal.calibrate(dets, 100)
+t_api = time.perf_counter() - t0
+# the oracle's linear stage on a sample of views (exactly linear in views up to the two small SVDs)
+sub = dets[:min(cpu_views, M)]
+t0 = time.perf_counter()
+lo.estimate_calibration_parameters(c["model"], sub)
+t_cpu = (time.perf_counter() - t0) * M / len(sub)
+print(json.dumps({"workload": name, "scale": scale, "views": M, "points": int(offs[-1]),
+                  "stages_ms": {k_: 1e3 * v for k_, v in best.items()}, "total_ms": 1e3 * sum(best.values()),
+                  "calibrate_api_ms": 1e3 * t_api, "lm_iterations": int(it), "sse": float(sse),
+                  "A": np.asarray(A).tolist(), "k": [float(x) for x in k],
+                  "A_true": np.asarray(c["A"]).tolist(), "k_true": [float(x) for x in c["k"]],
+                  "cpu_oracle_linear_stage_ms_scaled_from_sample": 1e3 * t_cpu, "cpu_sample_views": len(sub)}))

@@ -571,8 +571,9 @@ class Calibrator:
 
 
 def calibrateCamera(allDetections, distortionType, maxIters, initial=None, device=0):
-    """src/main.py:11-36 with the GPU refinement.  `initial` = (A, W, k) from the (CPU, closed
-    form) initial estimate; ValueError on an unknown distortion type as in the reference."""
+    """src/main.py:11-36 on the GPU path: closed-form initial estimate and LM refinement on one device
+    handle.  `initial` = (A, W, k) skips the estimate; ValueError on an unknown distortion type as in
+    the reference.  Returns (sse, Afinal, Wfinal, kFinal)."""
     model = distortion.model_id_of(distortionType)
     calibrator = Calibrator(model, device)
     return calibrator.calibrate(allDetections, maxIters, initial=initial)

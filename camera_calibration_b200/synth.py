@@ -56,6 +56,50 @@ def make_dataset(corners, A, k, model, width, height, numViews, noise_sigma=None
     return dets, poses
 
 
+def make_dataset_on_device(corners, A, k, model, width, height, numViews, noise_sigma=None,
+                           roll_pitch=(-30, 30), yaw=(-180, 180), dist=(0.5, 1.0), view_seed_base=0, device=0):
+    """The same generator with the projection of ALL views done by one
+    device pass (calib_project = Calibrator.projectAllPoints, the kernels' own point_eval) instead of
+    one numpy projectWithDistortion per view.  The seeded RNG stays on the host and is consumed in the
+    reference's order (pose draws, then the view's noise), so poses, noise and masks are the reference's;
+    the projected coordinates agree with the host path to rounding (<= 1e-9 px, tests), not bit for bit
+    -- the parity fixtures therefore keep using make_dataset."""
+    from . import calibrate
+    mid = distortion.model_id_of(model)
+    n = corners.shape[0]
+    poses = []
+    for viewIndex in range(numViews):
+        np.random.seed(view_seed_base + viewIndex)
+        aimIndex = np.random.choice(n)
+        rx = np.random.uniform(*roll_pitch)
+        ry = np.random.uniform(*roll_pitch)
+        rz = np.random.uniform(*yaw)
+        d = np.random.uniform(*dist)
+        poses.append(np.linalg.inv(_camera_pose_in_board(corners[aimIndex], (rx, ry, rz), d)))
+    W = np.array(poses)
+    offs = np.arange(numViews + 1, dtype=np.int64) * n
+    model_pts = np.tile(np.asarray(corners, dtype=np.float64), (numViews, 1))
+    prob = calibrate.Problem(mid, offs, model_pts, np.zeros((numViews * n, 2)), device)
+    try:
+        P = calibrate.Calibrator(mid, device)._composeParameterVector(A, poses, k).ravel()
+        u_all = prob.project(P).reshape(numViews, n, 2)
+    finally:
+        prob.close()
+    z_all = np.einsum("vj,nj->vn", W[:, 2, :3], corners) + W[:, 2, 3:4]      # camera-frame depth
+    dets = []
+    for viewIndex in range(numViews):
+        u = u_all[viewIndex]
+        if noise_sigma is not None:
+            np.random.seed(view_seed_base + viewIndex)      # replay the pose draws, then the noise
+            np.random.choice(n)
+            for rng in (roll_pitch, roll_pitch, yaw, dist):
+                np.random.uniform(*rng)
+            u = u + np.random.normal(0.0, noise_sigma, u.shape)
+        keep = ((u[:, 0] > 0) & (u[:, 0] < width) & (u[:, 1] > 0) & (u[:, 1] < height) & (z_all[viewIndex] > 0))
+        dets.append((u[keep], corners[keep]))
+    return dets, poses
+
+
 def perturbed_initial(A, k, poses, rs, rel_A=0.01, euler_deg=0.5, trans=0.005, zero_k=True):
     """Initial guess for sizes where the reference's O(N^2) linear stage cannot run
     (SURVEY.md section 8d): ground truth perturbed with a fixed RandomState."""

@@ -544,3 +544,34 @@ def test_full_size_cfg3_properties_and_oracle():
         parts += p2.cost(np.concatenate([P[:L], P[L + 6 * lo:L + 6 * hi]]))
         p2.close()
     assert abs(parts - last) < 1e-11 * last
+
+
+def test_calibrate_camera_from_json():
+    """main.calibrateCamera (src/main.py:11-36) fed from the reference's detections JSON: the user-facing
+    path end to end (file -> initial estimate -> refinement), ground truth recovered as in itest_main."""
+    import contextlib
+    import io
+    import os
+    from camera_calibration_b200 import dataset
+    dets = dataset.createDetectionsFromPath(os.path.join(os.path.dirname(__file__), "golden", "detections_cfg1.json"))
+    with contextlib.redirect_stdout(io.StringIO()):
+        sse, A, W, k = cc.calibrateCamera(dets, "radtan", 100)
+    c = synth.config("cfg1")
+    assert sse < 1e-10 and np.allclose(A, c["A"], atol=1e-9) and np.allclose(k, c["k"], atol=1e-9)
+    assert len(W) == len(dets) and W[0].shape == (4, 4)
+    with pytest.raises(ValueError):
+        cc.calibrateCamera(dets, "pinhole", 10)
+
+
+@pytest.mark.parametrize("model,k,sigma", [("radtan", synth.K_RADTAN, None), ("fisheye", synth.K_FISHEYE, 0.1)])
+def test_dataset_generation_on_device(model, k, sigma):
+    """Dataset._computeDetections / VirtualCamera._measurePoints (src/dataset.py:59-82,
+    src/virtualcamera.py:42-55) with the projection on the device: same poses, same in-image masks, same
+    noise as the host generator (which is bit-identical to the reference's), coordinates <= 1e-9 px."""
+    corners = synth.checkerboard_corners(9, 6, 0.050)
+    host, ph = synth.make_dataset(corners, synth.A_SYNTHETIC, k, model, 1440, 1080, 12, sigma)
+    dev, pd = synth.make_dataset_on_device(corners, synth.A_SYNTHETIC, k, model, 1440, 1080, 12, sigma)
+    assert len(host) == len(dev) == 12
+    for (sh, mh), (sd, md), a, b in zip(host, dev, ph, pd):
+        assert np.array_equal(a, b) and np.array_equal(mh, md)
+        assert sh.shape == sd.shape and np.abs(sh - sd).max() < 1e-9

@@ -113,3 +113,25 @@ def test_large_config_shapes():
     assert len(W0) == 10 and np.all(k0 == 0)
     b = synth.batch_config(2)
     assert len(b) == 2 and len(b[0]["dets"]) == 20
+
+
+def test_detections_json_wire_format(tmp_path):
+    """The detections JSON of the reference (src/dataset.py:97-109,133-141): the fixture was written by
+    the reference's own Dataset.exportDetections (oracle/make_golden_json.py); our reader returns the
+    cfg1 detections bit for bit and our writer reproduces the file byte for byte."""
+    import os
+    import numpy as np
+    from camera_calibration_b200 import dataset
+    here = os.path.dirname(__file__)
+    fixture = os.path.join(here, "golden", "detections_cfg1.json")
+    dets = dataset.createDetectionsFromPath(fixture)
+    g = np.load(os.path.join(here, "golden", "cfg1.npz"))
+    offs = g["view_offsets"]
+    assert len(dets) == len(offs) - 1
+    for v, (s, m) in enumerate(dets):
+        assert s.shape[1] == 2 and m.shape[1] == 3
+        assert np.array_equal(s, g["sensor_pts"][offs[v]:offs[v + 1]])
+        assert np.array_equal(m, g["model_pts"][offs[v]:offs[v + 1]])
+    out = tmp_path / "d.json"
+    dataset.exportDetections(dets, str(out))
+    assert open(out, "rb").read() == open(fixture, "rb").read()

@@ -1377,7 +1377,7 @@ extern "C" int calib_batch_create(calib_batch_t** out, int model, int64_t n_prob
     // shared memory: stage the detections when two blocks per SM still fit, else stream them from L2
     int stage = 1;
     BatchSmem lay = batch_smem_layout(L, (int)max_views, (int)max_points, 1);
-    if ((size_t)lay.total * 8 > 110 * 1024) { stage = 0; lay = batch_smem_layout(L, (int)max_views, (int)max_points, 0); }
+    if ((size_t)lay.total * 8 > (size_t)(220 / kBatchBlocks) * 1024) { stage = 0; lay = batch_smem_layout(L, (int)max_views, (int)max_points, 0); }
     if ((size_t)lay.total * 8 > 220 * 1024)
         return bfail(nullptr, CALIB_E_ARG, "calib_batch_create: a problem has too many views for the one-block-per-problem "
                                            "path (about 100); use calib_create for it");

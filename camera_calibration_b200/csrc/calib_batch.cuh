@@ -12,7 +12,14 @@
 
 namespace calib {
 
-constexpr int kBatchWarps = 4;
+#ifndef CALIB_BATCH_WARPS
+#define CALIB_BATCH_WARPS 4
+#endif
+#ifndef CALIB_BATCH_BLOCKS
+#define CALIB_BATCH_BLOCKS 2
+#endif
+constexpr int kBatchWarps = CALIB_BATCH_WARPS;        // warps per problem
+constexpr int kBatchBlocks = CALIB_BATCH_BLOCKS;      // problems resident per SM (register and shared-memory budget)
 constexpr int kBatchThreads = kBatchWarps * 32;
 constexpr int kBDStride = kNBD + 1;     // 97: odd stride in doubles -> conflict-free thread-per-view reads
 constexpr int kVtStride = kVtab + 1;    // 89
@@ -107,7 +114,7 @@ __device__ __forceinline__ void view_backsub_thread(const double* vt, const doub
 }
 
 template <int MODEL>
-__global__ void __launch_bounds__(kBatchThreads, 2) k_batch_lm(BatchDev d) {
+__global__ void __launch_bounds__(kBatchThreads, kBatchBlocks) k_batch_lm(BatchDev d) {
     using T = ModelTraits<MODEL>;
     constexpr int L = T::L, NT = L * (L + 1) / 2, NWE = NT + L;
     extern __shared__ __align__(16) double smem[];
@@ -202,36 +209,38 @@ __global__ void __launch_bounds__(kBatchThreads, 2) k_batch_lm(BatchDev d) {
                 if (lane == 0) sE[warp] = e;
             }
             __syncthreads();
-            if (tid < kNA) {
-                double s = sRedA[tid];
+            for (int t = tid; t <= kNA; t += kBatchThreads) {
+                if (t < kNA) {
+                    double s = sRedA[t];
 #pragma unroll
-                for (int k = 1; k < kBatchWarps; ++k) s += sRedA[k * kNA + tid];
-                sA[tid] = s;
-            } else if (tid == kNA) {
-                double s = sE[0];
+                    for (int k = 1; k < kBatchWarps; ++k) s += sRedA[k * kNA + t];
+                    sA[t] = s;
+                } else {
+                    double s = sE[0];
 #pragma unroll
-                for (int k = 1; k < kBatchWarps; ++k) s = __dadd_rn(s, sE[k]);
-                if (sInt[3] == 0) sScal[1] = s;      // later: the trial cost of the last accepted step
+                    for (int k = 1; k < kBatchWarps; ++k) s = __dadd_rn(s, sE[k]);
+                    if (sInt[3] == 0) sScal[1] = s;      // later: the trial cost of the last accepted step
+                }
             }
         }
         // Schur stage: one thread per view
         for (int v = tid; v < M; v += kBatchThreads) view_schur_thread<MODEL>(sBD + v * kBDStride, lam, sVt + v * kVtStride);
         __syncthreads();
         // W = sum_v Z_v^T Z_v and w = sum_v Z_v^T z_g: one thread per entry
-        if (tid < NWE) {
-            int e = tid, p, c;
+        for (int t = tid; t < NWE; t += kBatchThreads) {
+            int e = t, p, c;
             if (e < NT) { p = 0; while (e >= L - p) { e -= L - p; ++p; } c = p + e; }
             else { p = e - NT; c = L; }
             double s = 0.0;
             for (int v = 0; v < M; ++v) {
                 const double* zp = sVt + v * kVtStride + 21 + p * 6;
                 const double* zc = sVt + v * kVtStride + 21 + c * 6;
-                double t = 0.0;
+                double tt = 0.0;
 #pragma unroll
-                for (int i = 0; i < 6; ++i) t = fma(zp[i], zc[i], t);
-                s += t;
+                for (int i = 0; i < 6; ++i) tt = fma(zp[i], zc[i], tt);
+                s += tt;
             }
-            sW[tid] = s;
+            sW[t] = s;
         }
         __syncthreads();
         // reduced solve by warp 0 -> dc, trial shared parameters

@@ -1,5 +1,7 @@
 """Latency study: globaltimer stamps inside the four kernels of one pass (build with -DCALIB_STAMPS,
-see profiles/README.md).  usage: CALIB_B200_SO=.../libcalib_b200_stamps.so python profiles/stamps.py [cfg3] [scale]"""
+same nvcc line as camera_calibration_b200/_lib.py NVCC_FLAGS plus -DCALIB_STAMPS, output e.g.
+camera_calibration_b200/libcalib_b200_stamps.so; the product library carries no stamps).
+usage: CALIB_B200_SO=$PWD/camera_calibration_b200/libcalib_b200_stamps.so python profiles/stamps.py [cfg3] [scale]"""
 import ctypes
 import os
 import sys

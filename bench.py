@@ -426,6 +426,7 @@ def main():
     if world > 1:
         from camera_calibration_b200 import sharding
         transport = sharding.connect(prob, dist, args.transport)
+        prob.comm_set_default(local)
 
     def barrier():
         torch.cuda.synchronize()
@@ -461,9 +462,7 @@ def main():
 
     # ---- e2e: host buffers in, host buffers out, every step
     def e2e_step():
-        p2 = cc.Problem(model, offs, mp_pin, sp_pin, device=local)
-        if world > 1:
-            p2.comm_share(prob)
+        p2 = cc.Problem(model, offs, mp_pin, sp_pin, device=local)     # borrows prob's communicator (set_default)
         p2.set_ladder(args.ladder)
         p2.set_pdl(args.pdl)
         _, _, it, _ = p2.lm_run(Ploc, MAX_ITERS, want_trace=False)

@@ -116,6 +116,7 @@ def lib():
         "calib_comm_unique_id": (c_int, [_vp]),
         "calib_comm_init": (c_int, [_vp, c_int, c_int, _vp]),
         "calib_comm_share": (c_int, [_vp, _vp]),
+        "calib_comm_set_default": (c_int, [_vp, c_int]),
         "calib_peer_export": (c_int, [_vp, _vp]),
         "calib_peer_attach": (c_int, [_vp, c_int, c_int, _vp]),
         "calib_set_transport": (c_int, [_vp, c_int]),

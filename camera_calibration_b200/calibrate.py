@@ -275,6 +275,10 @@ class Problem:
             iters.ctypes.data_as(ctypes.POINTER(ctypes.c_int)), dptr(trace) if want_trace else None))
         return Hb.reshape(M, 3, 3), iters, trace
 
+    def comm_set_default(self, device, on=True):
+        """handles created on `device` from now on borrow this handle's communicators"""
+        self._check(self._L.calib_comm_set_default(self._h if on else None, int(device)))
+
     def peer_export(self) -> bytes:
         """64-byte CUDA IPC handle of this rank's inbox for the in-kernel all-reduce"""
         buf = ctypes.create_string_buffer(64)

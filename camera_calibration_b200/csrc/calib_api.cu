@@ -337,7 +337,12 @@ static int ensure_trace(calib_handle* h, int iters) {
     return CALIB_OK;
 }
 
-namespace { int build_loop_graph(calib_handle* h); }
+namespace {
+int build_loop_graph(calib_handle* h);
+void apply_transport(calib_handle* h);
+std::mutex g_default_mu;
+const calib_handle* g_default_comm[64] = {nullptr};   // per device: handle whose communicator new handles borrow
+}
 
 extern "C" const char* calib_last_error(const calib_t* h) {
     return h ? h->err.c_str() : g_last_error.c_str();
@@ -426,6 +431,15 @@ extern "C" int calib_create(calib_t** out, int model, int64_t M, const int64_t* 
 #undef TRY_
     int rc = build_tasks(h, 0, false);
     if (rc) { g_last_error = h->err; return bail(rc); }
+    {   // borrow the device's default communicator (calib_comm_set_default) before the graph is built
+        std::lock_guard<std::mutex> lk(g_default_mu);
+        const calib_handle* o = device_id < 64 ? g_default_comm[device_id] : nullptr;
+        if (o) {
+            h->comm = o->comm; h->comm_owned = false; h->nranks = o->nranks; h->rank = o->rank;
+            h->peer = o->peer; h->transport = o->transport;
+            apply_transport(h);
+        }
+    }
     // the default loop graph is built here, on the host, while the detections are still crossing PCIe
     // (a setting that changes the iteration drops it and lm_run rebuilds it)
     if (build_loop_graph(h) != CALIB_OK) { cudaGetLastError(); drop_graph(h); }
@@ -440,6 +454,10 @@ extern "C" int calib_create(calib_t** out, int model, int64_t M, const int64_t* 
 extern "C" void calib_destroy(calib_t* h) {
     if (!h) return;
     ScopeTimer tm_("calib_destroy");
+    {
+        std::lock_guard<std::mutex> lk(g_default_mu);
+        if (h->device < 64 && g_default_comm[h->device] == h) g_default_comm[h->device] = nullptr;
+    }
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     drop_graph(h);
@@ -1138,6 +1156,14 @@ extern "C" int calib_comm_share(calib_t* h, const calib_t* owner) {
     h->nranks = owner->nranks; h->rank = owner->rank;
     h->peer = owner->peer; h->transport = owner->transport;
     apply_transport(h);
+    return CALIB_OK;
+}
+
+extern "C" int calib_comm_set_default(const calib_t* owner, int device_id) {
+    if (device_id < 0 || device_id >= 64) return fail(nullptr, CALIB_E_ARG, "calib_comm_set_default: bad device_id");
+    if (owner && owner->device != device_id) return fail(nullptr, CALIB_E_ARG, "calib_comm_set_default: owner is on another device");
+    std::lock_guard<std::mutex> lk(g_default_mu);
+    g_default_comm[device_id] = owner;
     return CALIB_OK;
 }
 

@@ -153,22 +153,21 @@ __device__ __forceinline__ double solve_dense_core(double* S, int lane) {
 // numbers come from one function (calibrate.py:155-156).
 template <int MODEL, class Ld>
 __device__ __forceinline__ void solve_candidates(const Dev& d, const double* red, double* dense, int J, Ld ld) {
-    constexpr int L = ModelTraits<MODEL>::L, NE = L * L + L;
+    using T = ModelTraits<MODEL>;
+    constexpr int L = T::L, ND = T::ND, NE = L * L + L;
+    using SA = SlotsA<ND>;
     LmState* st = d.st;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const double lam0 = st->lam;
     const int cur = st->cur, iter = st->iter;
     double pcur = 0.0;
     if (warp < J && lane < L) pcur = d.Pbuf[(long long)cur * d.K + lane];
+    // dense S = A + lam diag(A) - W (L x L, row-major), then s = g_c - w (L), per candidate; red may be
+    // global memory (NCCL path), hence ld
     for (int e = tid; e < J * NE; e += (int)blockDim.x) {
-        const int j = e / NE;
+        const int j = e / NE, el = e - j * NE;
         double lam = lam0;
         for (int k = 0; k < j; ++k) lam = lam * 10.0;      // the reference's own update chain
-        // red may be global (NCCL path): go through ld
-        const int el = e - j * NE;
-        using T = ModelTraits<MODEL>;
-        constexpr int ND = T::ND;
-        using SA = SlotsA<ND>;
         const double* redA = red + kRedA;
         const double* redW = red + red_w(j);
         double out;

@@ -192,6 +192,10 @@ int calib_comm_init(calib_t* h, int nranks, int rank, const void* id128);
 /* Borrow the communicator of another handle of this process (it must outlive h): lets a
  * long-lived communicator serve one calib_create/calib_lm_run/calib_destroy per calibration. */
 int calib_comm_share(calib_t* h, const calib_t* owner);
+/* Every handle created on device_id from now on borrows owner's communicators (as calib_comm_share
+ * would, but before calib_create builds its loop graph); owner = NULL clears it.  Destroying the owner
+ * clears it too. */
+int calib_comm_set_default(const calib_t* owner, int device_id);
 
 /* The same exchange WITHOUT a library collective: the last thread block of the Schur kernel / the
  * cost kernel writes its 161-double reduced system (resp. the scalar trial cost) straight into every

@@ -36,6 +36,14 @@ def main():
     # a second run on the same communicator (sequence numbers carry on) must repeat the first bit for bit
     sse2, P2, iters2, tr2 = prob.lm_run(Ploc, 100)
     assert iters2 == iters and sse2 == sse and np.array_equal(P2, P) and np.array_equal(tr2, tr)
+    # a handle created afterwards borrows the communicator of the device's default owner
+    prob.comm_set_default(local)
+    p3 = cc.Problem(model, offs, mp, sp, device=local)
+    assert p3.transport() == prob.transport() != 0
+    sse3, P3, iters3, tr3 = p3.lm_run(Ploc, 100)
+    assert iters3 == iters and sse3 == sse and np.array_equal(P3, P) and np.array_equal(tr3, tr)
+    p3.close()
+    prob.comm_set_default(local, on=False)
     # gather the extrinsics of every rank on rank 0
     parts = [None] * world
     dist.all_gather_object(parts, (lo, hi, P.tolist(), sse, iters, tr.tolist()))

@@ -114,10 +114,19 @@ class ClockSampler:
                 "samples": len(self.rows), "power_w_max": max(pw) if pw else None}
 
 
+def host_threads():
+    """all the host threads this process may use (torchrun sets OMP_NUM_THREADS=1 for its children:
+    the CPU arms ask for the cores explicitly)"""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def oracle_full_run(model, offs, mp, sp, P0):
     import oracle_c
     t0 = time.perf_counter()
-    _, _, it, tr = oracle_c.lm(model, P0, offs, mp, sp, MAX_ITERS)
+    _, _, it, tr = oracle_c.lm(model, P0, offs, mp, sp, MAX_ITERS, nthreads=host_threads())
     dt = time.perf_counter() - t0
     evals = 1 + int(tr[:-1, 3].sum())
     return it, evals, dt
@@ -128,7 +137,7 @@ def cpu_baseline(model, offs, mp, sp, P0):
     a fraction of a second to a few seconds for every workload benched here)."""
     import oracle_c
     it, evals, dt = oracle_full_run(model, offs, mp, sp, P0)
-    return dict(value=it / dt, unit="LM iterations/s", cores=oracle_c.num_threads(), kind="port",
+    return dict(value=it / dt, unit="LM iterations/s", cores=host_threads(), kind="port",
                 sample=f"one complete LM run of the workload: {it} iterations, {evals} Jacobian passes, "
                        f"{dt:.2f} s; C restatement of the reference's path (oracle/calib_oracle.c, OpenMP)",
                 jacobian_rows_per_s=2.0 * offs[-1] * evals / dt)
@@ -171,7 +180,7 @@ def run_reference_arm(args):
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "jacobian_rows_per_sec": 2.0 * offs[-1] * evals / dt, "lm_iterations_per_step": tot_it / args.steps,
         "config": workload_config(args, c, offs),
-        "cpu_baseline": {"value": val, "unit": "LM iterations/s", "cores": oracle_c.num_threads(), "kind": "port",
+        "cpu_baseline": {"value": val, "unit": "LM iterations/s", "cores": host_threads(), "kind": "port",
                          "sample": "each step = one complete LM run of the workload; C restatement of the "
                                    "reference's path (oracle/calib_oracle.c, OpenMP over all host threads); the "
                                    "Python/sympy reference cannot travel to this box nor hold this workload's dense J"},

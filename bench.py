@@ -200,6 +200,20 @@ def ncu_traffic(workload, n_points):
         return None
 
 
+def fp64_issue(model, n_points, seconds, peak_tflops):
+    """Executed FP64 instructions (ncu count per point, profiles/r1w_fp64_mix.md) against the FP64 issue
+    rate the DFMA micro-benchmark reached: the kernel exploits more structure than the algorithmic FLOP
+    figure assumes, so this is the fraction of the pipe it really keeps busy."""
+    try:
+        ipp = float(json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+                    ["fp64_instructions_per_point_k_eval"][str(int(model))])
+    except Exception:
+        return None
+    issue_peak = peak_tflops * 1e12 / 2.0          # thread-level FP64 instructions per second
+    return {"instructions_per_point": ipp, "achieved_ginst_per_s": ipp * n_points / seconds / 1e9,
+            "peak_ginst_per_s": issue_peak / 1e9, "frac": ipp * n_points / seconds / issue_peak}
+
+
 def pinned_copy(L, arr):
     """numpy view of a page-locked copy of arr (calib_host_alloc); returns (view, ptr)."""
     ptr = L.calib_host_alloc(max(arr.nbytes, 8))
@@ -538,6 +552,7 @@ def main():
                 "avg_launch_us": avg_s * 1e6, "avg_launch_us_after_l2_flush": cold_s * 1e6,
                 "frac_after_l2_flush": fl / cold_s / 1e12 / peak64,
                 "fp64_pipe_active_pct_ncu": "see profiles/README.md (ncu sm__inst_executed_pipe_fp64)",
+                "fp64_issue": fp64_issue(model, n_loc, avg_s, peak64),
                 "hbm": {"achieved": by / cold_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
                         "frac": by / cold_s / 1e9 / hbm_peak, "bytes_per_point_per_sweep": BYTES_PER_POINT,
                         "peak_source": "MEASURED_PEAKS.json (of measured)" if peaks else "fallback 6650 (of fallback)"}}

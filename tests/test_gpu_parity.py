@@ -503,25 +503,29 @@ def test_calibrate_end_to_end_like_itest(golden):
 
 
 # ---- BASELINE full sizes: size-independent properties + the block-sparse oracle --------------------
-def test_full_size_cfg3_properties_and_oracle():
-    """cfg3 at its full size (1000 views x 40x40 grid, 1.55 M points, K = 6010): the dense reference
-    cannot hold J (154 GB).  Checked here: the C oracle's trace up to the plateau and iterate there
+@pytest.mark.parametrize("name,model_name", [("cfg3", "radtan"), ("cfg5", "fisheye")])
+def test_full_size_properties_and_oracle(name, model_name):
+    """cfg3 (1000 views x 40x40 grid, 1.55 M points, K = 6010) and cfg5 (10 000 views x 64x64 grid,
+    fisheye, 40.9 M points, K = 60 009; the trial-cost sweep goes through the TMA ring) at their full
+    sizes: the dense reference cannot hold J (154 GB / 28.8 GB for JTJ alone).  Checked here: the C oracle's trace up to the plateau and iterate there
     (<= 1e-8), and properties that hold at any size -- E(i+1) = E'(i) after every accepted step,
     accepted costs strictly decrease, calib_cost(P_final) reproduces the last accepted cost bit for bit,
     the gradient J^T r at the solution is ~0 relative to its start, the sum of the per-view block costs
     (each view refined alone is NOT needed: one calib_cost per half of the views) equals the whole."""
-    c = synth.config("cfg3", scale=1.0)
-    cal = cc.Calibrator("radtan")
+    c = synth.config(name, scale=1.0)
+    cal = cc.Calibrator(model_name)
+    mid = c["model"]
+    L = 10 if mid == 0 else 9
     P0 = cal._composeParameterVector(*c["init"]).ravel()
     offs, mp, sp = cc.flatten_detections(c["dets"])
     M = len(offs) - 1
-    prob = cc.Problem(0, offs, mp, sp)
+    prob = cc.Problem(mid, offs, mp, sp)
     sse, P, iters, tr = prob.lm_run(P0, 100)
-    so, Po, io, to = oc.lm(0, P0, offs, mp, sp, 100)
+    so, Po, io, to = oc.lm(mid, P0, offs, mp, sp, 100)
     stop = _check_trace(tr, to)
     assert stop >= 5
     _, Ps, _, _ = prob.lm_run(P0, stop)
-    _, Pso, _, _ = oc.lm(0, P0, offs, mp, sp, stop)
+    _, Pso, _, _ = oc.lm(mid, P0, offs, mp, sp, stop)
     assert param_relerr(Ps, Pso) < TOL_P
     assert abs(sse - so) < 1e-9 * so
     acc = tr[:, 3] == 1
@@ -536,11 +540,10 @@ def test_full_size_cfg3_properties_and_oracle():
     prob.close()
     # additivity over views: cost(all) = cost(first half) + cost(second half) to rounding
     h = M // 2
-    L = 10
     parts = 0.0
     for lo, hi in ((0, h), (h, M)):
         o2 = offs[lo:hi + 1] - offs[lo]
-        p2 = cc.Problem(0, o2, mp[offs[lo]:offs[hi]], sp[offs[lo]:offs[hi]])
+        p2 = cc.Problem(mid, o2, mp[offs[lo]:offs[hi]], sp[offs[lo]:offs[hi]])
         parts += p2.cost(np.concatenate([P[:L], P[L + 6 * lo:L + 6 * hi]]))
         p2.close()
     assert abs(parts - last) < 1e-11 * last

@@ -578,3 +578,30 @@ def test_dataset_generation_on_device(model, k, sigma):
     for (sh, mh), (sd, md), a, b in zip(host, dev, ph, pd):
         assert np.array_equal(a, b) and np.array_equal(mh, md)
         assert sh.shape == sd.shape and np.abs(sh - sd).max() < 1e-9
+
+
+def test_full_size_batch_cfg4():
+    """BASELINE config 4 at its full size: 8192 independent 20-view calibrations in one launch.  A
+    problem's result must not depend on the batch around it (bit-identical to the same problem run in a
+    batch of one -- checked on a sample), the oracle must agree on the sample, and over ALL problems:
+    iterations > 0, a finite cost that is below the cost at the initial guess, sse equal to the last
+    trace row's E."""
+    probs, P0 = _batch_inputs(8192)
+    bp = cc.BatchProblem(0, [p["dets"] for p in probs])
+    sse, P, iters, tr, ms = bp.lm_run(np.concatenate(P0), 100, want_trace=True)
+    slices = bp.param_slices()
+    bp.close()
+    assert np.all(iters > 0) and np.all(np.isfinite(sse))
+    last = tr[np.arange(len(iters)), iters - 1]
+    assert np.array_equal(sse, last[:, 0])
+    assert np.all(sse <= tr[:, 0, 0])
+    for j in (0, 1, 4095, 8191):
+        offs, mp, sp = cc.flatten_detections(probs[j]["dets"])
+        b1 = cc.BatchProblem(0, [probs[j]["dets"]])
+        s1, P1, i1, t1, _ = b1.lm_run(P0[j], 100, want_trace=True)
+        b1.close()
+        assert i1[0] == iters[j] and s1[0] == sse[j] and np.array_equal(P1, P[slices[j]])
+        assert np.array_equal(t1[0, :i1[0]], tr[j, :iters[j]])
+        so, Po, io, to = oc.lm(0, P0[j], offs, mp, sp, 100)
+        assert _check_trace(tr[j, :iters[j]], to) >= 5
+        assert abs(sse[j] - so) < 1e-9 * max(so, 1e-12) or (sse[j] < 1e-10 and so < 1e-10)

@@ -49,7 +49,7 @@ __host__ __device__ inline BatchSmem batch_smem_layout(int L, int max_views, int
     s.bd = o;    o += max_views * kBDStride;
     s.vt = o;    o += max_views * kVtStride;
     s.redA = o;  o += kBatchWarps * kNA + kNA + kNBD;     // per-warp A rows, summed A, W
-    s.misc = o;  o += 64;                                  // per-warp costs, dc, scalars
+    s.misc = o;  o += 64 + 112;                            // per-warp costs, dc, scalars; dense reduced system
     o = (o + 1) & ~1;
     s.pts = o;   o += stage_points ? 5 * max_points : 0;
     s.total = o;
@@ -140,6 +140,7 @@ __global__ void __launch_bounds__(kBatchThreads, kBatchBlocks) k_batch_lm(BatchD
     double* sdc = sE + 8;                                        // [L]
     double* sScal = sdc + 16;                                    // lam, E_cur, E_trial, sse
     int* sInt = reinterpret_cast<int*>(sScal + 8);               // cur, need_eval, done, iter
+    double* sDense = sE + 64;                                    // [L * L + L]
 
     // ---- set-up: parameters, view constants, detections
     for (int i = tid; i < K; i += kBatchThreads) sP[i] = gP[i];
@@ -243,9 +244,29 @@ __global__ void __launch_bounds__(kBatchThreads, kBatchBlocks) k_batch_lm(BatchD
             sW[t] = s;
         }
         __syncthreads();
-        // reduced solve by warp 0 -> dc, trial shared parameters
+        // reduced system in dense form by all threads (the slot bookkeeping of the structured A block is
+        // off the serial chain), solved by warp 0 -> dc, trial shared parameters
+        {
+            using SA = SlotsA<T::ND>;
+            for (int e = tid; e < L * L + L; e += kBatchThreads) {
+                double out;
+                if (e < L * L) {
+                    const int i = e / L, c = e - i * L;
+                    const int lo = i < c ? i : c, hi = i < c ? c : i;
+                    const int sl = a_slot<T::ND>(lo, hi);
+                    double v = sl >= 0 ? sA[sl] : 0.0;
+                    if (i == c) v = fma(lam, v, v);
+                    out = v - sW[tri(L, lo, hi)];
+                } else {
+                    const int i = e - L * L;
+                    out = sA[SA::G + i] - sW[L * (L + 1) / 2 + i];
+                }
+                sDense[e] = out;
+            }
+        }
+        __syncthreads();
         if (warp == 0) {
-            const double dc = solve_reduced_core<MODEL>(sA, sW, lam, lane, LdPlain());
+            const double dc = solve_dense_core<L>(sDense, lane);
             if (lane < L) { sdc[lane] = dc; Pt[lane] = Pc[lane] + dc; }
         }
         __syncthreads();

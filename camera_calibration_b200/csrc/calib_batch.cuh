@@ -56,10 +56,10 @@ __host__ __device__ inline BatchSmem batch_smem_layout(int L, int max_views, int
     return s;
 }
 
-// Per-view Schur stage by ONE thread: bd = the view's summed (B_v | D_v | g_v) row, vt = out row
-// (packed strictly-lower factor with 1/diagonal on the diagonal, then Z column by column).
+// Per-view Schur stage in two steps.  Factor: ONE thread per view (bd = the view's summed
+// (B_v | D_v | g_v) row; vt gets the packed strictly-lower factor with 1/diagonal on the diagonal).
 template <int MODEL>
-__device__ __forceinline__ void view_schur_thread(const double* bd, double lam, double* vt) {
+__device__ __forceinline__ void view_factor_thread(const double* bd, double lam, double* vt) {
     constexpr int L = ModelTraits<MODEL>::L;
     using S = SlotsBD<L>;
     double Lc[36], id[6];
@@ -76,19 +76,24 @@ __device__ __forceinline__ void view_schur_thread(const double* bd, double lam, 
     for (int a = 0; a < 6; ++a)
 #pragma unroll
         for (int b = 0; b <= a; ++b) vt[a * (a + 1) / 2 + b] = (a == b) ? id[a] : Lc[a * 6 + b];
-#pragma unroll 1
-    for (int c = 0; c <= L; ++c) {
-        const double* rhs = bd + ((c < L) ? (S::B + c * 6) : S::GV);
-        double z[6];
+}
+
+// Forward substitution L z = column c of [B_v^T | g_v]: one thread per (view, column), so the L + 1
+// columns of a view are solved side by side instead of one after the other by the factoring thread.
+template <int MODEL>
+__device__ __forceinline__ void view_column_thread(const double* bd, int c, double* vt) {
+    constexpr int L = ModelTraits<MODEL>::L;
+    using S = SlotsBD<L>;
+    const double* rhs = bd + ((c < L) ? (S::B + c * 6) : S::GV);
+    double z[6];
 #pragma unroll
-        for (int i = 0; i < 6; ++i) {
-            double s = rhs[i];
+    for (int i = 0; i < 6; ++i) {
+        double s = rhs[i];
 #pragma unroll
-            for (int k = 0; k < 6; ++k)
-                if (k < i) s = fma(-Lc[i * 6 + k], z[k], s);
-            z[i] = s * id[i];
-            vt[21 + c * 6 + i] = z[i];
-        }
+        for (int k = 0; k < 6; ++k)
+            if (k < i) s = fma(-vt[i * (i + 1) / 2 + k], z[k], s);
+        z[i] = s * vt[i * (i + 1) / 2 + i];
+        vt[21 + c * 6 + i] = z[i];
     }
 }
 
@@ -225,7 +230,12 @@ __global__ void __launch_bounds__(kBatchThreads, kBatchBlocks) k_batch_lm(BatchD
             }
         }
         // Schur stage: one thread per view
-        for (int v = tid; v < M; v += kBatchThreads) view_schur_thread<MODEL>(sBD + v * kBDStride, lam, sVt + v * kVtStride);
+        for (int v = tid; v < M; v += kBatchThreads) view_factor_thread<MODEL>(sBD + v * kBDStride, lam, sVt + v * kVtStride);
+        __syncthreads();
+        for (int it = tid; it < M * (L + 1); it += kBatchThreads) {
+            const int v = it / (L + 1), c = it - v * (L + 1);
+            view_column_thread<MODEL>(sBD + v * kBDStride, c, sVt + v * kVtStride);
+        }
         __syncthreads();
         // W = sum_v Z_v^T Z_v and w = sum_v Z_v^T z_g: one thread per entry
         for (int t = tid; t < NWE; t += kBatchThreads) {

@@ -91,6 +91,7 @@ def lib():
         "calib_set_pdl": (c_int, [_vp, c_int]),
         "calib_host_alloc": (_vp, [ctypes.c_size_t]),
         "calib_host_free": (None, [_vp]),
+        "calib_host_gather": (c_int, [_vp, _vp, _i64, c_i64, c_int]),
         "calib_project": (c_int, [_vp, _d, _d]),
         "calib_cost": (c_int, [_vp, _d, _d]),
         "calib_eval_residual_jacobian": (c_int, [_vp, _d, _d, _d, _d]),

@@ -32,6 +32,8 @@ def flatten_detections(allDetections, out=None):
     else:
         model, sensor = out[0][:N], out[1][:N]
     if N:
+        if N >= 100000 and _gather_fast(allDetections, counts, model, sensor):
+            return offs, model, sensor
         try:
             np.concatenate([m for s, m in allDetections], axis=0, out=model)
             np.concatenate([s for s, m in allDetections], axis=0, out=sensor)
@@ -40,6 +42,30 @@ def flatten_detections(allDetections, out=None):
                 model[offs[i]:offs[i + 1]] = np.asarray(m, dtype=np.float64).reshape(-1, 3)
                 sensor[offs[i]:offs[i + 1]] = np.asarray(s, dtype=np.float64).reshape(-1, 2)
     return offs, model, sensor
+
+
+def _gather_fast(allDetections, counts, model, sensor):
+    """Large inputs: threaded gather in the library (calib_host_gather) when every per-view array is a
+    C-contiguous float64 array of the expected shape; False = let numpy do it."""
+    f8 = np.dtype(np.float64)
+    M = len(allDetections)
+    pm = np.empty(M, dtype=np.uint64)
+    ps = np.empty(M, dtype=np.uint64)
+    for i, (s, m) in enumerate(allDetections):
+        if not (type(m) is np.ndarray and type(s) is np.ndarray and m.dtype == f8 and s.dtype == f8
+                and m.ndim == 2 and s.ndim == 2 and m.shape[1] == 3 and s.shape[1] == 2 and len(s) == len(m)
+                and m.flags.c_contiguous and s.flags.c_contiguous):
+            return False
+        pm[i] = m.__array_interface__["data"][0]
+        ps[i] = s.__array_interface__["data"][0]
+    try:
+        L = _lib.lib()
+    except CalibError:
+        return False
+    i64 = ctypes.POINTER(ctypes.c_int64)
+    bm, bs = counts * 24, counts * 16
+    ok = L.calib_host_gather(model.ctypes.data, pm.ctypes.data, bm.ctypes.data_as(i64), M, 0) == 0
+    return ok and L.calib_host_gather(sensor.ctypes.data, ps.ctypes.data, bs.ctypes.data_as(i64), M, 0) == 0
 
 
 class PinnedBuffers:

@@ -12,6 +12,7 @@
 #include <cstring>
 #include <memory>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/calib_b200.h"
@@ -510,6 +511,35 @@ extern "C" int calib_set_cost_staging(calib_t* h, int mode) {
     if (mode < -1 || mode > 1) return fail(h, CALIB_E_ARG, "calib_set_cost_staging: -1 auto, 0 loads, 1 bulk copies");
     if (h->cost_tma != mode) drop_graph(h);
     h->cost_tma = mode;
+    return CALIB_OK;
+}
+
+// Host-side helper of the Python mirror: concatenates the per-view arrays of allDetections (a list of
+// separately allocated numpy arrays) into one buffer with a few threads -- numpy's concatenate is one
+// thread and, at 60 MB, costs more than the whole refinement.
+extern "C" int calib_host_gather(void* dst, const void* const* srcs, const int64_t* bytes, int64_t n, int nthreads) {
+    if (!dst || !srcs || !bytes || n < 0) return fail(nullptr, CALIB_E_ARG, "calib_host_gather: bad args");
+    std::vector<size_t> off((size_t)n + 1, 0);
+    for (int64_t i = 0; i < n; ++i) {
+        if (bytes[i] < 0 || (bytes[i] > 0 && !srcs[i])) return fail(nullptr, CALIB_E_ARG, "calib_host_gather: bad piece");
+        off[i + 1] = off[i] + (size_t)bytes[i];
+    }
+    const size_t total = off[(size_t)n];
+    int T = nthreads > 0 ? nthreads : (int)std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency()));
+    if (total < ((size_t)4 << 20)) T = 1;
+    auto work = [&](int t) {
+        const size_t lo = total * (size_t)t / (size_t)T, hi = total * (size_t)(t + 1) / (size_t)T;   // byte range of thread t
+        size_t i = (size_t)(std::upper_bound(off.begin(), off.end(), lo) - off.begin()) - 1;
+        for (; i < (size_t)n && off[i] < hi; ++i) {
+            const size_t a = std::max(off[i], lo), b = std::min(off[i + 1], hi);
+            if (b > a) memcpy((char*)dst + a, (const char*)srcs[i] + (a - off[i]), b - a);
+        }
+    };
+    if (T == 1) { work(0); return CALIB_OK; }
+    std::vector<std::thread> th;
+    for (int t = 1; t < T; ++t) th.emplace_back(work, t);
+    work(0);
+    for (auto& x : th) x.join();
     return CALIB_OK;
 }
 

@@ -93,6 +93,10 @@ int calib_set_cost_staging(calib_t* h, int mode);
  * (optional: any host pointer works, pinned ones copy at full PCIe rate).  NULL on failure. */
 void* calib_host_alloc(size_t bytes);
 void calib_host_free(void* p);
+/* Concatenates n separately allocated host arrays (srcs[i], bytes[i]) into dst with a few threads: the
+ * per-view arrays of the reference's allDetections list (src/dataset.py:31-34) -> the CSR buffers of
+ * calib_create.  nthreads <= 0: automatic.  Host only; no device needed. */
+int calib_host_gather(void* dst, const void* const* srcs, const int64_t* bytes, int64_t n, int nthreads);
 
 /* Calibrator.projectAllPoints, src/calibrate.py:190-197.  y: N x 2. */
 int calib_project(calib_t* h, const double* P, double* y);

@@ -135,3 +135,27 @@ def test_detections_json_wire_format(tmp_path):
     out = tmp_path / "d.json"
     dataset.exportDetections(dets, str(out))
     assert open(out, "rb").read() == open(fixture, "rb").read()
+
+
+def test_flatten_detections_threaded_gather():
+    """flatten_detections on a large list goes through calib_host_gather (threads in the library, no
+    device involved) and must equal numpy's concatenate; odd inputs (float32, non-contiguous, lists)
+    take the numpy path and give the same CSR arrays."""
+    import numpy as np
+    import camera_calibration_b200 as cc
+    rs = np.random.RandomState(3)
+    dets = []
+    for v in range(300):
+        n = int(rs.randint(1, 900))
+        dets.append((rs.rand(n, 2), rs.rand(n, 3)))
+    dets[7] = (dets[7][0][:0], dets[7][1][:0])                      # an empty view
+    offs, m, s = cc.flatten_detections(dets)
+    assert offs[-1] >= 100000
+    assert np.array_equal(m, np.concatenate([d[1] for d in dets])) and np.array_equal(s, np.concatenate([d[0] for d in dets]))
+    assert np.array_equal(np.diff(offs), [len(d[1]) for d in dets])
+    odd = list(dets)
+    odd[3] = (np.asfortranarray(dets[3][0]), dets[3][1][::1].astype(np.float32))
+    odd[5] = (dets[5][0].tolist(), dets[5][1].tolist())
+    o2, m2, s2 = cc.flatten_detections(odd)
+    assert np.array_equal(o2, offs) and np.array_equal(s2, s)
+    assert np.allclose(m2, m, rtol=1e-6)

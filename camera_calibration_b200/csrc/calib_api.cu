@@ -5,11 +5,13 @@
 #include <nccl.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <mutex>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
 #include <memory>
 #include <string>
 #include <thread>
@@ -349,8 +351,128 @@ extern "C" const char* calib_last_error(const calib_t* h) {
     return h ? h->err.c_str() : g_last_error.c_str();
 }
 
-extern "C" int calib_create(calib_t** out, int model, int64_t M, const int64_t* view_offsets,
-                            const double* model_pts, const double* sensor_pts, int device_id) {
+// ---- detections held as per-view arrays: gather and upload, pipelined ---------------------------
+namespace {
+
+constexpr size_t kGatherChunk = (size_t)1 << 20;   // bytes per staged piece
+constexpr int kGatherThreads = 8;                   // at most; each with two staging slots
+constexpr int kGatherDefault = 4;                   // 4 x ~13 GB/s of memcpy keeps up with the PCIe copies; 8 measured slower
+
+struct GatherPool {                                 // per device; created on first use, kept
+    std::mutex mu;
+    char* pinned = nullptr;
+    cudaStream_t stream[kGatherThreads] = {};
+    cudaEvent_t slot_free[kGatherThreads][2] = {};
+    cudaEvent_t done[kGatherThreads] = {};
+    bool ok = false;
+};
+GatherPool g_gather[64];
+
+cudaError_t gather_pool_init(GatherPool& g) {
+    if (g.ok) return cudaSuccess;
+    cudaError_t e = cudaHostAlloc((void**)&g.pinned, kGatherThreads * 2 * kGatherChunk, cudaHostAllocPortable);
+    if (e != cudaSuccess) return e;
+    for (int t = 0; t < kGatherThreads && e == cudaSuccess; ++t) {
+        e = cudaStreamCreateWithFlags(&g.stream[t], cudaStreamNonBlocking);
+        for (int k = 0; k < 2 && e == cudaSuccess; ++k) e = cudaEventCreateWithFlags(&g.slot_free[t][k], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&g.done[t], cudaEventDisableTiming);
+    }
+    g.ok = e == cudaSuccess;
+    return e;
+}
+
+// Copies `bytes` bytes starting at byte `lo` of the concatenation of the views' arrays (stride bytes per
+// point) into dst.
+void gather_range(char* dst, const double* const* ptrs, const int64_t* offs, int64_t M, size_t stride, size_t lo, size_t bytes) {
+    const size_t hi = lo + bytes;
+    int64_t i = (std::upper_bound(offs, offs + M + 1, (int64_t)(lo / stride)) - offs) - 1;
+    for (; i < M && (size_t)offs[i] * stride < hi; ++i) {
+        const size_t a = std::max((size_t)offs[i] * stride, lo), b = std::min((size_t)offs[i + 1] * stride, hi);
+        if (b > a) memcpy(dst + (a - lo), (const char*)ptrs[i] + (a - (size_t)offs[i] * stride), b - a);
+    }
+}
+
+// model points -> aos_model (N x 3), sensor points -> aos_sensor (N x 2), both device and ready to be
+// written.  Touches none of the caller's streams (it runs beside a stream capture of the creating thread):
+// the copies go out on the pool's streams, *n_streams of them; upload_views_join orders a stream after them.
+cudaError_t upload_views(int device, const int64_t* offs, int64_t M, const double* const* vm,
+                         const double* const* vs, double* aos_model, double* aos_sensor, int* n_streams) {
+    GatherPool& g = g_gather[device < 64 ? device : 63];
+    std::lock_guard<std::mutex> lk(g.mu);
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = gather_pool_init(g);
+    if (e != cudaSuccess) return e;
+    const size_t N = (size_t)offs[M];
+    const size_t bytes_m = N * 24, bytes_s = N * 16;
+    const size_t cm = (bytes_m + kGatherChunk - 1) / kGatherChunk, cs = (bytes_s + kGatherChunk - 1) / kGatherChunk;
+    const size_t nchunks = cm + cs;
+    int T = kGatherDefault;
+    if (const char* ev = getenv("CALIB_GATHER_THREADS")) T = std::max(1, std::min(kGatherThreads, atoi(ev)));
+    T = (int)std::min<size_t>({(size_t)T, nchunks, (size_t)std::max(1u, std::thread::hardware_concurrency())});
+    *n_streams = std::max(T, 1);
+    std::atomic<size_t> next{0};
+    std::atomic<int> err{(int)cudaSuccess};
+    ScopeTimer tm_all("upload_views (helper thread)");
+    const bool timing = debug_timing();
+    double t_gather[kGatherThreads] = {}, t_wait[kGatherThreads] = {}, t_issue[kGatherThreads] = {}, t_start[kGatherThreads] = {};
+    const auto t_zero = std::chrono::steady_clock::now();
+    auto us_since = [](std::chrono::steady_clock::time_point a) {
+        return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - a).count();
+    };
+    auto work = [&](int t) {
+        if (timing) t_start[t] = us_since(t_zero);
+        cudaError_t r = cudaSetDevice(device);
+        for (int k = 0; r == cudaSuccess; ++k) {
+            const size_t c = next.fetch_add(1);
+            if (c >= nchunks) break;
+            const bool is_m = c < cm;
+            const size_t lo = (is_m ? c : c - cm) * kGatherChunk;
+            const size_t n = std::min(kGatherChunk, (is_m ? bytes_m : bytes_s) - lo);
+            char* slot = g.pinned + ((size_t)t * 2 + (k & 1)) * kGatherChunk;
+            auto ta = std::chrono::steady_clock::now();
+            r = cudaEventSynchronize(g.slot_free[t][k & 1]);   // the copy that last used this slot (any call) has left it
+            if (r != cudaSuccess) break;
+            if (timing) { t_wait[t] += us_since(ta); ta = std::chrono::steady_clock::now(); }
+            gather_range(slot, is_m ? vm : vs, offs, M, is_m ? 24 : 16, lo, n);
+            if (timing) { t_gather[t] += us_since(ta); ta = std::chrono::steady_clock::now(); }
+            r = cudaMemcpyAsync((char*)(is_m ? aos_model : aos_sensor) + lo, slot, n, cudaMemcpyHostToDevice, g.stream[t]);
+            if (r == cudaSuccess) r = cudaEventRecord(g.slot_free[t][k & 1], g.stream[t]);
+            if (timing) t_issue[t] += us_since(ta);
+        }
+        if (r == cudaSuccess) r = cudaEventRecord(g.done[t], g.stream[t]);
+        if (r != cudaSuccess) err.store((int)r);
+    };
+    if (T <= 1) work(0);
+    else {
+        std::vector<std::thread> th;
+        for (int t = 1; t < T; ++t) th.emplace_back(work, t);
+        work(0);
+        for (auto& x : th) x.join();
+    }
+    if (timing)
+        for (int t = 0; t < std::max(T, 1); ++t)
+            fprintf(stderr, "[calib]   gather thread %2d: start +%.0f us, wait %.0f, gather %.0f, issue %.0f us\n", t, t_start[t],
+                    t_wait[t], t_gather[t], t_issue[t]);
+    if (err.load() != (int)cudaSuccess) {
+        for (int t = 0; t < std::max(T, 1); ++t) cudaStreamSynchronize(g.stream[t]);
+        return (cudaError_t)err.load();
+    }
+    return cudaSuccess;   // copies still in flight: the slot events guard the staging against the next call
+}
+
+cudaError_t upload_views_join(int device, cudaStream_t stream, int n_streams) {
+    GatherPool& g = g_gather[device < 64 ? device : 63];
+    for (int t = 0; t < n_streams; ++t) {
+        cudaError_t e = cudaStreamWaitEvent(stream, g.done[t], 0);
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
+}  // namespace
+
+static int create_impl(calib_t** out, int model, int64_t M, const int64_t* view_offsets, const double* model_pts,
+                       const double* sensor_pts, const double* const* vmodel, const double* const* vsensor, int device_id) {
     if (!out) return fail(nullptr, CALIB_E_ARG, "calib_create: out is NULL");
     *out = nullptr;
     if (model != CALIB_MODEL_RADTAN && model != CALIB_MODEL_FISHEYE)
@@ -361,7 +483,7 @@ extern "C" int calib_create(calib_t** out, int model, int64_t M, const int64_t* 
         if (view_offsets[v + 1] < view_offsets[v])
             return fail(nullptr, CALIB_E_ARG, "calib_create: view_offsets not non-decreasing");
     const int64_t N = view_offsets[M];
-    if (N > 0 && (!model_pts || !sensor_pts)) return fail(nullptr, CALIB_E_ARG, "calib_create: NULL points");
+    if (N > 0 && !vmodel && (!model_pts || !sensor_pts)) return fail(nullptr, CALIB_E_ARG, "calib_create: NULL points");
     if (N >= (1ll << 31) - 64 || M >= (1ll << 27)) return fail(nullptr, CALIB_E_ARG, "calib_create: too large");
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0)
@@ -373,6 +495,10 @@ extern "C" int calib_create(calib_t** out, int model, int64_t M, const int64_t* 
     h->M = M; h->N = N; h->K = h->L + 6 * M;
     h->view_offsets.assign(view_offsets, view_offsets + M + 1);
     auto bail = [&](int rc) { calib_destroy(h); return rc; };
+    std::thread uploader;
+    cudaError_t upload_rc = cudaSuccess;
+    int upload_streams = 0;
+    std::function<cudaError_t()> repack;
 #define TRY_(call) do { int rc__ = [&]() -> int { CUDA_TRY(h, call); return 0; }(); if (rc__) { g_last_error = h->err; return bail(rc__); } } while (0)
     TRY_(cudaSetDevice(device_id));
     pool_keep_memory(device_id);
@@ -422,16 +548,27 @@ extern "C" int calib_create(calib_t** out, int model, int64_t M, const int64_t* 
         TRY_(cudaMemsetAsync(a.base + zero_from, 0, zero_bytes, h->stream));
         if (N > 0) {
             double* aos = a.at<double>(o_aos);
-            TRY_(cudaMemcpyAsync(aos, model_pts, (size_t)N * 3 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-            TRY_(cudaMemcpyAsync(aos + 3 * n, sensor_pts, (size_t)N * 2 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-            const int nb = (int)std::min<int64_t>((N + 255) / 256, (int64_t)h->n_sm * 8);
-            k_repack<<<nb, 256, 0, h->stream>>>(aos, aos + 3 * n, N, soa, soa + n, soa + 2 * n, soa + 3 * n, soa + 4 * n);
-            TRY_(cudaGetLastError());
+            repack = [=]() {
+                const int nb = (int)std::min<int64_t>((N + 255) / 256, (int64_t)h->n_sm * 8);
+                k_repack<<<nb, 256, 0, h->stream>>>(aos, aos + 3 * n, N, soa, soa + n, soa + 2 * n, soa + 3 * n, soa + 4 * n);
+                return cudaGetLastError();
+            };
+            if (vmodel) {
+                // gather + copies run on helper threads (the copies on their own streams, after everything
+                // enqueued so far) while this thread builds the partition and the loop graph below
+                TRY_(cudaStreamSynchronize(h->stream));   // allocation + memset done: the helper streams need no edge
+                uploader = std::thread([=, &upload_rc, &upload_streams]() {
+                    upload_rc = upload_views(device_id, h->view_offsets.data(), M, vmodel, vsensor, aos, aos + 3 * n, &upload_streams);
+                });
+            } else {
+                TRY_(cudaMemcpyAsync(aos, model_pts, (size_t)N * 3 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+                TRY_(cudaMemcpyAsync(aos + 3 * n, sensor_pts, (size_t)N * 2 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+                TRY_(repack());
+            }
         }
     }
-#undef TRY_
     int rc = build_tasks(h, 0, false);
-    if (rc) { g_last_error = h->err; return bail(rc); }
+    if (rc) { if (uploader.joinable()) uploader.join(); g_last_error = h->err; return bail(rc); }
     {   // borrow the device's default communicator (calib_comm_set_default) before the graph is built
         std::lock_guard<std::mutex> lk(g_default_mu);
         const calib_handle* o = device_id < 64 ? g_default_comm[device_id] : nullptr;
@@ -444,12 +581,39 @@ extern "C" int calib_create(calib_t** out, int model, int64_t M, const int64_t* 
     // the default loop graph is built here, on the host, while the detections are still crossing PCIe
     // (a setting that changes the iteration drops it and lm_run rebuilds it)
     if (build_loop_graph(h) != CALIB_OK) { cudaGetLastError(); drop_graph(h); }
+    if (uploader.joinable()) {
+        uploader.join();
+        TRY_(upload_rc);
+        TRY_(upload_views_join(device_id, h->stream, upload_streams));
+        TRY_(repack());
+    }
+#undef TRY_
     {   // the caller's buffers are free again once the stream is idle
         cudaError_t e = cudaStreamSynchronize(h->stream);
         if (e != cudaSuccess) { h->err = cudaGetErrorString(e); g_last_error = h->err; return bail(CALIB_E_CUDA); }
     }
     *out = h;
     return CALIB_OK;
+}
+
+extern "C" int calib_create(calib_t** out, int model, int64_t M, const int64_t* view_offsets,
+                            const double* model_pts, const double* sensor_pts, int device_id) {
+    return create_impl(out, model, M, view_offsets, model_pts, sensor_pts, nullptr, nullptr, device_id);
+}
+
+extern "C" int calib_create_from_views(calib_t** out, int model, int64_t M, const int64_t* counts,
+                                       const double* const* model_ptrs, const double* const* sensor_ptrs, int device_id) {
+    if (out) *out = nullptr;
+    if (M <= 0 || !counts || !model_ptrs || !sensor_ptrs)
+        return fail(nullptr, CALIB_E_ARG, "calib_create_from_views: need M >= 1 views, counts and pointers");
+    std::vector<int64_t> offs((size_t)M + 1, 0);
+    for (int64_t v = 0; v < M; ++v) {
+        if (counts[v] < 0) return fail(nullptr, CALIB_E_ARG, "calib_create_from_views: negative count");
+        if (counts[v] > 0 && (!model_ptrs[v] || !sensor_ptrs[v]))
+            return fail(nullptr, CALIB_E_ARG, "calib_create_from_views: NULL points in a non-empty view");
+        offs[v + 1] = offs[v] + counts[v];
+    }
+    return create_impl(out, model, M, offs.data(), nullptr, nullptr, model_ptrs, sensor_ptrs, device_id);
 }
 
 extern "C" void calib_destroy(calib_t* h) {

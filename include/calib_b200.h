@@ -53,6 +53,14 @@ const char* calib_last_error(const calib_t* h);
  * Replaces the per-iteration Python lists of src/calibrate.py:138-139,277-282. */
 int calib_create(calib_t** out, int model, int64_t M, const int64_t* view_offsets,
                  const double* model_pts, const double* sensor_pts, int device_id);
+/* The same from the reference's own container: allDetections is a list of per-view (sensorPoints
+ * (N_i,2), modelPoints (N_i,3)) arrays (src/dataset.py:31-34, src/calibrate.py:277-282), each its own
+ * allocation.  counts[i] = N_i; model_ptrs[i] / sensor_ptrs[i] = the C-contiguous float64 data of view i
+ * (may be NULL where N_i = 0).  The views are gathered into page-locked staging owned by the library by a
+ * few host threads, chunk by chunk, while the previous chunks cross PCIe -- the caller never builds the
+ * concatenated copy.  Results are identical to calib_create on the concatenated arrays. */
+int calib_create_from_views(calib_t** out, int model, int64_t M, const int64_t* counts,
+                            const double* const* model_ptrs, const double* const* sensor_ptrs, int device_id);
 void calib_destroy(calib_t* h);
 
 int64_t calib_num_params(const calib_t* h);  /* K = L + 6M */

@@ -54,3 +54,16 @@ def cabi():
 
 
 t("C-ABI create+lm_run+destroy (pinned CSR)", cabi, n=5)
+
+
+def views():
+    p = cc.Problem.from_detections(c["model"], c["dets"])
+    r = p.lm_run(P0, 100, want_trace=False)
+    p.close()
+    return r
+
+
+from camera_calibration_b200 import calibrate as _cal  # noqa: E402
+t("_view_pointers (per-view addresses)", lambda: _cal._view_pointers(c["dets"]), n=5)
+t("from_detections+lm_run+destroy (per-view arrays)", views, n=5)
+t("Calibrator.refineCalibrationParameters (again)", lambda: cal.refineCalibrationParameters(A0, W0, k0, c["dets"], 100), n=5)

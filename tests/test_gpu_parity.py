@@ -605,3 +605,57 @@ def test_full_size_batch_cfg4():
         so, Po, io, to = oc.lm(0, P0[j], offs, mp, sp, 100)
         assert _check_trace(tr[j, :iters[j]], to) >= 5
         assert abs(sse[j] - so) < 1e-9 * max(so, 1e-12) or (sse[j] < 1e-10 and so < 1e-10)
+
+
+@pytest.mark.gpu
+def test_create_from_views_matches_flat_upload(golden):
+    """calib_create_from_views (the reference's list of per-view arrays, gathered and uploaded by the
+    library in pipelined chunks) must leave exactly the detections calib_create gets from the
+    concatenated arrays: projections, costs and a whole LM run are bit-identical.  Sizes on both sides
+    of the 2 MB chunk, ragged and empty views, read-only arrays, and the numpy fallback for odd inputs."""
+    g = golden("cfg1")
+    offs = g["view_offsets"]
+    dets = [(g["sensor_pts"][offs[i]:offs[i + 1]].copy(), g["model_pts"][offs[i]:offs[i + 1]].copy())
+            for i in range(len(offs) - 1)]
+    flat = cc.Problem(0, offs, g["model_pts"], g["sensor_pts"])
+    views = cc.Problem.from_detections(0, dets)
+    assert views.M == flat.M and views.N == flat.N and np.array_equal(views.view_offsets, offs)
+    assert np.array_equal(views.project(g["P0"]), flat.project(g["P0"]))
+    ra, rb = flat.lm_run(g["P0"], 100), views.lm_run(g["P0"], 100)
+    assert ra[0] == rb[0] and np.array_equal(ra[1], rb[1]) and np.array_equal(ra[3], rb[3])
+    flat.close(), views.close()
+    # read-only arrays and the list fallback
+    ro = [(s.copy(), m.copy()) for s, m in dets]
+    for s, m in ro:
+        s.flags.writeable = False
+        m.flags.writeable = False
+    odd = [(s.tolist(), m.tolist()) for s, m in dets]
+    for d in (ro, odd):
+        p = cc.Problem.from_detections(0, d)
+        r = p.lm_run(g["P0"], 100)
+        assert r[0] == ra[0] and np.array_equal(r[1], ra[1])
+        p.close()
+    # several chunks per array, views that straddle chunk boundaries, an empty view
+    c = synth.config("cfg3", 0.25)
+    big = list(c["dets"])
+    big[5] = (big[5][0][:0], big[5][1][:0])
+    offs2, mp, sp = cc.flatten_detections(big)
+    assert mp.nbytes > 3 * (2 << 20)
+    P0 = cc.Calibrator(c["model"])._composeParameterVector(*c["init"])
+    a, b = cc.Problem(c["model"], offs2, mp, sp), cc.Problem.from_detections(c["model"], big)
+    assert np.array_equal(a.project(P0), b.project(P0))
+    assert a.cost(P0) == b.cost(P0)
+    a.close()
+    b2 = cc.Problem.from_detections(c["model"], big)       # staging slots reused straight away
+    assert np.array_equal(b.project(P0), b2.project(P0))
+    b.close(), b2.close()
+    with pytest.raises(cc.CalibError):
+        L = cc._lib.lib()
+        import ctypes
+        h = ctypes.c_void_p()
+        cnt = np.array([3], dtype=np.int64)
+        nul = np.zeros(1, dtype=np.uint64)
+        rc = L.calib_create_from_views(ctypes.byref(h), 0, 1, cnt.ctypes.data_as(ctypes.POINTER(ctypes.c_int64)),
+                                       nul.ctypes.data, nul.ctypes.data, 0)
+        assert rc == -1 and not h
+        raise cc.CalibError(rc, L.calib_last_error(None).decode())

@@ -159,3 +159,28 @@ def test_flatten_detections_threaded_gather():
     o2, m2, s2 = cc.flatten_detections(odd)
     assert np.array_equal(o2, offs) and np.array_equal(s2, s)
     assert np.allclose(m2, m, rtol=1e-6)
+
+
+def test_view_pointers_of_detection_lists():
+    """calibrate._view_pointers: addresses and counts of the per-view arrays handed to
+    calib_create_from_views; anything that is not a C-contiguous float64 (n,2)/(n,3) pair -> None
+    (the numpy concatenate path takes over)."""
+    import ctypes
+    import numpy as np
+    from camera_calibration_b200 import calibrate
+    rs = np.random.RandomState(5)
+    dets = [(rs.rand(n, 2), rs.rand(n, 3)) for n in (4, 0, 7, 1)]
+    dets[2][1].flags.writeable = False                                # read-only: the slower pointer route
+    counts, pm, ps = calibrate._view_pointers(dets)
+    assert counts.tolist() == [4, 0, 7, 1] and counts.dtype == np.int64
+    for i, (s, m) in enumerate(dets):
+        if len(m):
+            assert pm[i] == m.ctypes.data and ps[i] == s.ctypes.data
+            assert np.array_equal(np.ctypeslib.as_array(ctypes.cast(int(pm[i]), ctypes.POINTER(ctypes.c_double)), (len(m) * 3,)), m.ravel())
+    assert calibrate._view_pointers([]) is None
+    assert calibrate._view_pointers([(dets[0][0].tolist(), dets[0][1])]) is None
+    assert calibrate._view_pointers([(dets[0][0], dets[0][1].astype(np.float32))]) is None
+    assert calibrate._view_pointers([(dets[0][0], np.asfortranarray(dets[0][1]))]) is None
+    assert calibrate._view_pointers([(dets[0][0][:3], dets[0][1])]) is None
+    wide = rs.rand(4, 6)
+    assert calibrate._view_pointers([(dets[0][0], wide[:, :3])]) is None

@@ -30,6 +30,9 @@ __device__ __forceinline__ void sweep(const Dev& d, const Piece* __restrict__ pi
 }
 
 // ---- the fused evaluation pass ----------------------------------------------------------------
+#ifndef CALIB_EVAL_PF
+#define CALIB_EVAL_PF 1   // register prefetch depth of the two sweeps
+#endif
 template <int MODEL>
 __global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
     using T = ModelTraits<MODEL>;
@@ -58,7 +61,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
         double acc[kNBD];
 #pragma unroll
         for (int i = 0; i < kNBD; ++i) acc[i] = 0.0;
-        sweep<false, 1, 1, 1, 1>(d, d.ev_piece, rec, views, sview[warp], warp, nullptr, lane,
+        sweep<false, 1, 1, 1, CALIB_EVAL_PF>(d, d.ev_piece, rec, views, sview[warp], warp, nullptr, lane,
             [&](const Piece&, int) {},
             [&](const Pt& p) {
                 PointOut<MODEL> o;
@@ -81,7 +84,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
 #pragma unroll
         for (int i = 0; i < kNA; ++i) acc[i] = 0.0;
         double e = 0.0;
-        sweep<false, 1, 1, 1, 1>(d, d.ev_piece, rec, views, sview[warp], warp, nullptr, lane,
+        sweep<false, 1, 1, 1, CALIB_EVAL_PF>(d, d.ev_piece, rec, views, sview[warp], warp, nullptr, lane,
             [&](const Piece&, int) {},
             [&](const Pt& p) {
                 PointOut<MODEL> o;

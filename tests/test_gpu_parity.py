@@ -659,3 +659,35 @@ def test_create_from_views_matches_flat_upload(golden):
                                        nul.ctypes.data, nul.ctypes.data, 0)
         assert rc == -1 and not h
         raise cc.CalibError(rc, L.calib_last_error(None).decode())
+
+
+def test_fisheye_wide_angle_vs_oracle():
+    """Fisheye points far off the axis (r = |(x,y)|/z up to ~8, where the device atan takes its
+    pi/2 - atan(1/r) branch) and close to it: projection, residuals and Jacobian against the numpy
+    oracle at the parity tolerance; a point ON the axis gives NaN in both (src/distortion.py:215)."""
+    rs = np.random.RandomState(21)
+    M, n = 6, 400
+    offs = np.arange(M + 1) * n
+    pts = np.zeros((M * n, 3))
+    ang = rs.uniform(0, 2 * np.pi, M * n)
+    rad = np.concatenate([rs.uniform(1e-4, 0.3, M * n // 2), rs.uniform(0.3, 8.0, M * n - M * n // 2)])
+    pts[:, 0], pts[:, 1] = rad * np.cos(ang), rad * np.sin(ang)
+    intr = np.array([420.0, 415.0, 0.3, 640.0, 512.0, -0.03, 0.004, -0.0007, 0.0001])
+    ext = np.column_stack([rs.uniform(-3, 3, M), rs.uniform(-3, 3, M), rs.uniform(-20, 20, M),
+                           rs.uniform(-0.02, 0.02, M), rs.uniform(-0.02, 0.02, M), rs.uniform(0.9, 1.1, M)])
+    P = np.concatenate([intr, ext.ravel()])
+    prob = cc.Problem(1, offs, pts, np.zeros((M * n, 2)))
+    y = prob.project(P)
+    y_ref = onp.project(1, P, offs, pts)
+    assert np.abs(y - y_ref).max() <= 1e-11 * np.abs(y_ref).max()
+    r, Jc, Jv = prob.residual_jacobian(P)
+    Jc_ref, Jv_ref = onp.jacobian_blocks(1, P, offs, pts)
+    assert jac_relerr(Jc, np.asarray(Jc_ref).reshape(Jc.shape)) < TOL_J
+    assert jac_relerr(Jv, np.asarray(Jv_ref).reshape(Jv.shape)) < TOL_J
+    prob.close()
+    on_axis = np.zeros((1, 3))
+    P1 = np.concatenate([intr, [0, 0, 0, 0, 0, 1.0]])
+    prob = cc.Problem(1, np.array([0, 1]), on_axis, np.zeros((1, 2)))
+    with np.errstate(all="ignore"):
+        assert np.isnan(prob.project(P1)).all() and np.isnan(onp.project(1, P1, np.array([0, 1]), on_axis)).all()
+    prob.close()

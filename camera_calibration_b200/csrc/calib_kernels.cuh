@@ -254,6 +254,68 @@ __device__ __forceinline__ void sweep_pieces(const Dev& d, const Piece* __restri
     }
 }
 
+// The same sweep with the per-point work split in two stages, software-pipelined inside a piece:
+// stage1 (the dependent chain: projection, distortion, residual) of point i+1 is issued together with
+// stage2 (the independent accumulations) of point i.  With two warps per scheduler the chain of the
+// second evaluation sweep is otherwise not covered (58 % FP64 issue); the accumulation order per lane is
+// unchanged, so the sums are bit-identical to sweep_pieces.  EXPERIMENT (-DCALIB_EVAL_STAGED=1), not the
+// default: at 255 registers ptxas does not interleave the stages and the copies cost 4 % (cfg3 k_eval
+// 63.8 against 61.2 us, profiles/r1z_staged.txt).
+template <int NV, class Begin, class Stage1, class Stage2, class End>
+__device__ __forceinline__ void sweep_pieces_staged(const Dev& d, const Piece* __restrict__ pieces, const WarpRec& rec,
+                                                    const ViewC* const (&views)[NV], ViewC (&sview)[NV], int lane,
+                                                    Begin begin, Stage1 stage1, Stage2 stage2, End end) {
+    const int p0 = rec.p0, p1 = rec.p1;
+    if (p0 >= p1) return;
+    Piece cur = rec.first;
+    Pt pn;
+    if (lane < cur.count) load_point(d, (long long)cur.start + lane, pn);
+    double vn[NV];
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+        vn[j] = 0.0;
+        if (lane < kViewDoubles) vn[j] = reinterpret_cast<const double*>(views[j] + cur.view)[lane];
+    }
+    for (int pi = p0; pi < p1; ++pi) {
+        const bool has_next = pi + 1 < p1;
+        Piece nxt = cur;
+        if (has_next) nxt = pieces[pi + 1];
+        __syncwarp();
+        if (lane < kViewDoubles) {
+#pragma unroll
+            for (int j = 0; j < NV; ++j) reinterpret_cast<double*>(&sview[j])[lane] = vn[j];
+        }
+        __syncwarp();
+        if (has_next && lane < kViewDoubles) {
+#pragma unroll
+            for (int j = 0; j < NV; ++j) vn[j] = reinterpret_cast<const double*>(views[j] + nxt.view)[lane];
+        }
+        begin(cur, pi);
+        if (lane >= cur.count && has_next && lane < nxt.count) load_point(d, (long long)nxt.start + lane, pn);
+        int i = lane;
+        if (i < cur.count) {
+            auto fetch = [&](int at) {
+                if (at + 32 < cur.count) load_point(d, (long long)cur.start + at + 32, pn);
+                else if (has_next && lane < nxt.count) load_point(d, (long long)nxt.start + lane, pn);
+            };
+            Pt p = pn;
+            fetch(i);
+            auto prev = stage1(p);
+            for (i += 32; i < cur.count; i += 32) {
+                p = pn;
+                fetch(i);
+                const auto o = stage1(p);
+                stage2(prev);
+                prev = o;
+            }
+            stage2(prev);
+        }
+        __syncwarp();
+        end(cur, pi);
+        cur = nxt;
+    }
+}
+
 // ---- view constants for parameter buffer `which` (start of a run) ---------------------------
 __global__ void k_make_views(Dev d, int which_is_cur) {
     const int v = blockIdx.x * blockDim.x + threadIdx.x;

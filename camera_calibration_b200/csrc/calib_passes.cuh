@@ -30,6 +30,9 @@ __device__ __forceinline__ void sweep(const Dev& d, const Piece* __restrict__ pi
 }
 
 // ---- the fused evaluation pass ----------------------------------------------------------------
+#ifndef CALIB_EVAL_STAGED
+#define CALIB_EVAL_STAGED 0   // 1: second sweep software-pipelined (sweep_pieces_staged); measured slower, r1z_staged.txt
+#endif
 #ifndef CALIB_EVAL_PF
 #define CALIB_EVAL_PF 1   // register prefetch depth of the two sweeps
 #endif
@@ -84,6 +87,17 @@ __global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
 #pragma unroll
         for (int i = 0; i < kNA; ++i) acc[i] = 0.0;
         double e = 0.0;
+#if CALIB_EVAL_STAGED
+        sweep_pieces_staged<1>(d, d.ev_piece, rec, views, sview[warp], lane,
+            [&](const Piece&, int) {},
+            [&](const Pt& p) {
+                PointOut<MODEL> o;
+                point_eval<MODEL, true, false>(sc, sview[warp][0], p.X, p.Y, p.Z, p.U, p.V, o);
+                return o;
+            },
+            [&](const PointOut<MODEL>& o) { accum_A<MODEL>(o, acc, e); },
+            [&](const Piece&, int) {});
+#else
         sweep<false, 1, 1, 1, CALIB_EVAL_PF>(d, d.ev_piece, rec, views, sview[warp], warp, nullptr, lane,
             [&](const Piece&, int) {},
             [&](const Pt& p) {
@@ -92,6 +106,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
                 accum_A<MODEL>(o, acc, e);
             },
             [&](const Piece&, int) {});
+#endif
         warp_reduce_scatter<kNA>(acc, lane);
         e = warp_sum(e);
         sred[warp][2 * lane] = acc[0];

@@ -230,6 +230,48 @@ static void drop_graph(calib_handle* h) {
     if (h->loop_graph) { cudaGraphExecDestroy(h->loop_graph); h->loop_graph = nullptr; }
 }
 
+// Tearing down an instantiated loop graph costs ~0.12 ms of host time, as much as everything else in
+// calib_destroy together times ten.  A destroyed handle parks its graphs here; the next calib_create on
+// that device destroys them while its detections cross PCIe (nothing else to do on the host then).  At
+// most kTrashMax graphs wait; beyond that the oldest are destroyed on the spot.
+struct TrashedGraph { int device; cudaGraphExec_t exec; };
+static std::mutex g_trash_mu;
+static std::vector<TrashedGraph> g_trash;
+constexpr size_t kTrashMax = 8;
+
+static void empty_trash(int device, size_t keep) {   // device < 0: any
+    std::vector<TrashedGraph> doomed;
+    {
+        std::lock_guard<std::mutex> lk(g_trash_mu);
+        std::vector<TrashedGraph> rest;
+        size_t excess = g_trash.size() > keep ? g_trash.size() - keep : 0;
+        for (const TrashedGraph& t : g_trash) {
+            if (excess && (device < 0 || t.device == device)) { doomed.push_back(t); --excess; }
+            else rest.push_back(t);
+        }
+        g_trash.swap(rest);
+    }
+    if (doomed.empty()) return;
+    int cur = 0;
+    cudaGetDevice(&cur);
+    for (const TrashedGraph& t : doomed) {
+        if (t.device != cur) cudaSetDevice(cur = t.device);
+        cudaGraphExecDestroy(t.exec);
+    }
+}
+
+static void park_graphs(calib_handle* h) {
+    {
+        std::lock_guard<std::mutex> lk(g_trash_mu);
+        if (h->graph) g_trash.push_back({h->device, h->graph});
+        if (h->loop_graph) g_trash.push_back({h->device, h->loop_graph});
+    }
+    h->graph = nullptr; h->loop_graph = nullptr;
+    const int dev = h->device;
+    empty_trash(-1, kTrashMax);
+    cudaSetDevice(dev);
+}
+
 // Cuts the N points into n_warps contiguous, near-equal chunks (one per persistent warp) and each
 // chunk into pieces at the view boundaries.
 static void cut_points(const std::vector<int64_t>& offs, int64_t M, int64_t N, int n_warps,
@@ -581,6 +623,7 @@ static int create_impl(calib_t** out, int model, int64_t M, const int64_t* view_
     // the default loop graph is built here, on the host, while the detections are still crossing PCIe
     // (a setting that changes the iteration drops it and lm_run rebuilds it)
     if (build_loop_graph(h) != CALIB_OK) { cudaGetLastError(); drop_graph(h); }
+    empty_trash(device_id, 0);      // graphs of destroyed handles: torn down while the detections cross PCIe
     if (uploader.joinable()) {
         uploader.join();
         TRY_(upload_rc);
@@ -625,7 +668,7 @@ extern "C" void calib_destroy(calib_t* h) {
     }
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
-    drop_graph(h);
+    park_graphs(h);       // destroyed by the next calib_create, under its upload
     if (h->comm && h->comm_owned && g_nccl.ok) g_nccl.CommDestroy(h->comm);
     for (auto& pe : h->prof_events) { cudaEventDestroy(pe.second.first); cudaEventDestroy(pe.second.second); }
     if (h->arena_part && h->stream) cudaFreeAsync(h->arena_part, h->stream);
@@ -1074,7 +1117,10 @@ extern "C" int calib_lm_run(calib_t* h, double* P_inout, int maxIters, double la
     int iters = 0;
     RC(calib_lm_run_resident(h, maxIters, lam0, lam_min, lam_max, err_min, sse_out, &iters));
     if (iters_out) *iters_out = iters;
-    if (trace) RC(calib_download_trace(h, iters, trace));
+    if (trace) {      // both downloads behind one synchronisation
+        if (iters > h->trace_cap) return fail(h, CALIB_E_ARG, "calib_lm_run: trace longer than its buffer");
+        CUDA_TRY(h, cudaMemcpyAsync(trace, h->dev.trace, (size_t)iters * 4 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    }
     return calib_download_params(h, P_inout);
 }
 

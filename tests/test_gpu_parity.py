@@ -691,3 +691,31 @@ def test_fisheye_wide_angle_vs_oracle():
     with np.errstate(all="ignore"):
         assert np.isnan(prob.project(P1)).all() and np.isnan(onp.project(1, P1, np.array([0, 1]), on_axis)).all()
     prob.close()
+
+
+def test_many_handles_created_and_destroyed(golden):
+    """Handles come and go (the e2e path creates one per refinement): destroyed handles park their
+    loop graphs for the next calib_create to tear down, streams and events are recycled.  Forty
+    create / run / destroy rounds over three problems, some destroyed out of order, give the same
+    answers as the first round, and more than the parked-graph bound are never kept."""
+    gs = [golden(n) for n in ("cfg1", "cfg2", "itest")]
+    first = {}
+    held = []
+    for k in range(40):
+        g = gs[k % 3]
+        prob = _problem(g)
+        sse, P, iters, tr = prob.lm_run(g["P0"], 30)
+        key = k % 3
+        if key in first:
+            assert sse == first[key][0] and iters == first[key][2] and np.array_equal(P, first[key][1])
+        else:
+            first[key] = (sse, P, iters)
+        if k % 5 == 0:
+            held.append(prob)          # destroyed later, out of order
+        else:
+            prob.close()
+    for prob in reversed(held):
+        prob.close()
+    prob = _problem(gs[0])
+    assert prob.lm_run(gs[0]["P0"], 30)[0] == first[0][0]
+    prob.close()

@@ -487,8 +487,12 @@ cudaError_t upload_views(int device, const int64_t* offs, int64_t M, const doubl
     if (T <= 1) work(0);
     else {
         std::vector<std::thread> th;
-        for (int t = 1; t < T; ++t) th.emplace_back(work, t);
+        std::vector<int> inline_t;                 // a thread that could not be started: its share runs here
+        for (int t = 1; t < T; ++t) {
+            try { th.emplace_back(work, t); } catch (...) { inline_t.push_back(t); }
+        }
         work(0);
+        for (int t : inline_t) work(t);
         for (auto& x : th) x.join();
     }
     if (timing)
@@ -540,6 +544,7 @@ static int create_impl(calib_t** out, int model, int64_t M, const int64_t* view_
     std::thread uploader;
     cudaError_t upload_rc = cudaSuccess;
     int upload_streams = 0;
+    bool upload_inline = false;
     std::function<cudaError_t()> repack;
 #define TRY_(call) do { int rc__ = [&]() -> int { CUDA_TRY(h, call); return 0; }(); if (rc__) { g_last_error = h->err; return bail(rc__); } } while (0)
     TRY_(cudaSetDevice(device_id));
@@ -599,9 +604,10 @@ static int create_impl(calib_t** out, int model, int64_t M, const int64_t* view_
                 // gather + copies run on helper threads (the copies on their own streams, after everything
                 // enqueued so far) while this thread builds the partition and the loop graph below
                 TRY_(cudaStreamSynchronize(h->stream));   // allocation + memset done: the helper streams need no edge
-                uploader = std::thread([=, &upload_rc, &upload_streams]() {
+                auto run_upload = [=, &upload_rc, &upload_streams]() {
                     upload_rc = upload_views(device_id, h->view_offsets.data(), M, vmodel, vsensor, aos, aos + 3 * n, &upload_streams);
-                });
+                };
+                try { uploader = std::thread(run_upload); } catch (...) { run_upload(); upload_inline = true; }
             } else {
                 TRY_(cudaMemcpyAsync(aos, model_pts, (size_t)N * 3 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
                 TRY_(cudaMemcpyAsync(aos + 3 * n, sensor_pts, (size_t)N * 2 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
@@ -624,8 +630,8 @@ static int create_impl(calib_t** out, int model, int64_t M, const int64_t* view_
     // (a setting that changes the iteration drops it and lm_run rebuilds it)
     if (build_loop_graph(h) != CALIB_OK) { cudaGetLastError(); drop_graph(h); }
     empty_trash(device_id, 0);      // graphs of destroyed handles: torn down while the detections cross PCIe
-    if (uploader.joinable()) {
-        uploader.join();
+    if (uploader.joinable() || upload_inline) {
+        if (uploader.joinable()) uploader.join();
         TRY_(upload_rc);
         TRY_(upload_views_join(device_id, h->stream, upload_streams));
         TRY_(repack());
@@ -744,8 +750,12 @@ extern "C" int calib_host_gather(void* dst, const void* const* srcs, const int64
     };
     if (T == 1) { work(0); return CALIB_OK; }
     std::vector<std::thread> th;
-    for (int t = 1; t < T; ++t) th.emplace_back(work, t);
+    std::vector<int> inline_t;
+    for (int t = 1; t < T; ++t) {
+        try { th.emplace_back(work, t); } catch (...) { inline_t.push_back(t); }
+    }
     work(0);
+    for (int t : inline_t) work(t);
     for (auto& x : th) x.join();
     return CALIB_OK;
 }

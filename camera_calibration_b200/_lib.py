@@ -114,6 +114,7 @@ def lib():
         "calib_refine_homographies": (c_int, [_vp, _d, c_int, c_dbl, c_dbl, c_dbl, c_dbl,
                                               ctypes.POINTER(c_int), _d]),
         "calib_dlt_gram": (c_int, [_vp, _d, _d]),
+        "calib_dlt_homographies": (c_int, [_vp, _d]),
         "calib_distortion_rows": (c_int, [_vp, _d, _d, _d]),
         "calib_comm_unique_id": (c_int, [_vp]),
         "calib_comm_init": (c_int, [_vp, c_int, c_int, _vp]),

@@ -1536,8 +1536,13 @@ int linear_call(calib_handle* h, int which, const double* A9, const double* W12,
         d.X = h->dev.X; d.Y = h->dev.Y; d.Z = h->dev.Z; d.U = h->dev.U; d.V = h->dev.V;
         d.offs = d_offs; d.M = (int)M; d.model = h->model;
         const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>(((int64_t)M + kBlockWarps - 1) / kBlockWarps, 8 * h->n_sm));
-        if (which == 0) {
-            d.gram = d0; d.norm = d1;
+        if (which == 0 || which == 2) {
+            if (which == 0) { d.gram = d0; d.norm = d1; }
+            else {          // the homographies are what leaves the device; Gram sums and normalisations stay
+                CUDA_TRY(h, dalloc(tmp, &d.gram, M * kGramN));
+                CUDA_TRY(h, dalloc(tmp, &d.norm, M * kNormN));
+                d.Hdlt = d0;
+            }
             k_dlt_gram<<<blocks, kBlockThreads, 0, h->stream>>>(d);
         } else {
             CUDA_TRY(h, dalloc(tmp, &dA, 9));
@@ -1562,6 +1567,12 @@ extern "C" int calib_dlt_gram(calib_t* h, double* gram, double* norm) {
     RC(check_handle(h));
     if (!gram || !norm) return fail(h, CALIB_E_ARG, "calib_dlt_gram: NULL output");
     return linear_call(h, 0, nullptr, nullptr, gram, kGramN, norm, kNormN);
+}
+
+extern "C" int calib_dlt_homographies(calib_t* h, double* H) {
+    RC(check_handle(h));
+    if (!H) return fail(h, CALIB_E_ARG, "calib_dlt_homographies: NULL output");
+    return linear_call(h, 2, nullptr, nullptr, H, 9, nullptr, 0);
 }
 
 extern "C" int calib_distortion_rows(calib_t* h, const double* A, const double* W, double* rows) {

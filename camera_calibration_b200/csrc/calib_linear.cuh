@@ -32,12 +32,66 @@ struct LinDev {
     const double* A;            // 9: intrinsic matrix, row-major
     const double* W;            // M x 12: R row-major, then t
     double* drows;              // M x kDistN: per-view sums of D^T D (upper triangle) and D^T Ddot
+    double* Hdlt;               // M x 9 or NULL: k_dlt_gram also solves for the homography
 };
 
 constexpr int kDistN = 20;      // radtan: 15 + 5; fisheye: 10 + 4 (padded)
 
+// Eigen-decomposition of a symmetric 9 x 9 matrix by one warp: cyclic Jacobi rotations on A (shared memory,
+// overwritten: eigenvalues on its diagonal), eigenvectors accumulated in the columns of V.  Lane k < 9 owns
+// row k.  A rotation is skipped when |a_pq| <= eps sqrt(|a_pp a_qq|) (the relative criterion that keeps the
+// small eigenvalues of a positive semi-definite matrix accurate); done when a whole sweep skipped everything.
+// Returns the index of the smallest eigenvalue.
+__device__ __forceinline__ int warp_jacobi9(double (*A)[9], double (*V)[9], int lane) {
+    if (lane < 9) {
+#pragma unroll
+        for (int j = 0; j < 9; ++j) V[lane][j] = lane == j ? 1.0 : 0.0;
+    }
+    __syncwarp();
+    for (int sweep = 0; sweep < 30; ++sweep) {
+        int rotated = 0;
+        for (int p = 0; p < 8; ++p) {
+            for (int q = p + 1; q < 9; ++q) {
+                const double apq = A[p][q], app = A[p][p], aqq = A[q][q];
+                if (!(fabs(apq) > 1e-17 * sqrt(fabs(app * aqq)))) continue;      // warp-uniform
+                rotated = 1;
+                const double theta = (aqq - app) / (2.0 * apq);
+                const double t = copysign(1.0, theta) / (fabs(theta) + sqrt(fma(theta, theta, 1.0)));
+                const double c = rsqrt(fma(t, t, 1.0)), sn = t * c;
+                __syncwarp();
+                if (lane < 9) {
+                    const double vp = V[lane][p], vq = V[lane][q];
+                    V[lane][p] = fma(c, vp, -sn * vq);
+                    V[lane][q] = fma(sn, vp, c * vq);
+                    if (lane != p && lane != q) {
+                        const double akp = A[lane][p], akq = A[lane][q];
+                        const double np_ = fma(c, akp, -sn * akq), nq = fma(sn, akp, c * akq);
+                        A[lane][p] = np_; A[p][lane] = np_;
+                        A[lane][q] = nq; A[q][lane] = nq;
+                    } else if (lane == p) {
+                        A[p][p] = fma(-t, apq, app);
+                        A[q][q] = fma(t, apq, aqq);
+                        A[p][q] = 0.0; A[q][p] = 0.0;
+                    }
+                }
+                __syncwarp();
+            }
+        }
+        if (!rotated) break;
+    }
+    int best = 0;
+    double lo = A[0][0];
+#pragma unroll
+    for (int j = 1; j < 9; ++j) {
+        const double e = A[j][j];
+        if (e < lo) { lo = e; best = j; }
+    }
+    return best;
+}
+
 __global__ void __launch_bounds__(kBlockThreads) k_dlt_gram(LinDev d) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __shared__ double sG[kBlockWarps][9][9], sVec[kBlockWarps][9][9];
     for (int v = blockIdx.x * kBlockWarps + warp; v < d.M; v += gridDim.x * kBlockWarps) {
         const long long p0 = d.offs[v], p1 = d.offs[v + 1];
         const double n = (double)(p1 - p0);
@@ -79,6 +133,62 @@ __global__ void __launch_bounds__(kBlockThreads) k_dlt_gram(LinDev d) {
             for (int k = 0; k < kGramN; ++k) d.gram[(long long)v * kGramN + k] = acc[k];
             double* nm = d.norm + (long long)v * kNormN;
             nm[0] = mu_; nm[1] = mv; nm[2] = sa; nm[3] = mx; nm[4] = my; nm[5] = sb;
+        }
+        if (d.Hdlt) {
+            // M^T M = [[P1, 0, -Pu], [0, P1, -Pv], [-Pu, -Pv, Pq]] with the 3 x 3 blocks P* = sums of w p p^T
+            // (acc[6 k ..] = packed 00 01 02 11 12 22); its eigenvector of the smallest eigenvalue is the
+            // normalised homography (src/linearcalibrate.py:52-56), then H = Na^-1 H' Nb, H /= H[2,2] (:57-58)
+            double (*G)[9] = sG[warp];
+            double (*E)[9] = sVec[warp];
+            double* sums = &E[0][0];                 // scratch until the rotations start
+            __syncwarp();
+            if (lane == 0) {
+#pragma unroll
+                for (int k = 0; k < kGramN; ++k) sums[k] = acc[k];
+            }
+            __syncwarp();
+            if (lane < 9) {
+                const int bi = lane / 3, i = lane % 3;
+#pragma unroll
+                for (int j = 0; j < 9; ++j) {
+                    const int bj = j / 3, jj = j % 3;
+                    const int a = i < jj ? i : jj, b = i < jj ? jj : i;
+                    const int pk = a * 3 - a * (a - 1) / 2 + (b - a);     // packed index of (a, b), a <= b
+                    double g = 0.0;
+                    if (bi == bj && bi < 2) g = sums[pk];
+                    else if (bi == 2 && bj == 2) g = sums[18 + pk];
+                    else if (bi + bj == 2 && bi != bj) g = -sums[6 + pk];      // blocks (0,2), (2,0): -Pu
+                    else if (bi + bj == 3) g = -sums[12 + pk];                  // blocks (1,2), (2,1): -Pv
+                    G[lane][j] = g;
+                }
+            }
+            __syncwarp();
+            const int jmin = warp_jacobi9(G, E, lane);
+            __syncwarp();
+            if (lane == 0) {
+                double hp[9];
+#pragma unroll
+                for (int k = 0; k < 9; ++k) hp[k] = E[k][jmin];
+                // Na^-1 = [[1/sa, 0, mu], [0, 1/sa, mv], [0, 0, 1]] ; Nb = [[sb, 0, -sb mx], [0, sb, -sb my], [0, 0, 1]]
+                double t[9], Hh[9];
+                const double isa = 1.0 / sa;
+#pragma unroll
+                for (int j = 0; j < 3; ++j) {
+                    t[j] = fma(isa, hp[j], mu_ * hp[6 + j]);
+                    t[3 + j] = fma(isa, hp[3 + j], mv * hp[6 + j]);
+                    t[6 + j] = hp[6 + j];
+                }
+#pragma unroll
+                for (int r = 0; r < 3; ++r) {
+                    Hh[3 * r + 0] = t[3 * r + 0] * sb;
+                    Hh[3 * r + 1] = t[3 * r + 1] * sb;
+                    Hh[3 * r + 2] = fma(-sb * mx, t[3 * r + 0], fma(-sb * my, t[3 * r + 1], t[3 * r + 2]));
+                }
+                const double ih = 1.0 / Hh[8];
+#pragma unroll
+                for (int k = 0; k < 9; ++k) d.Hdlt[(long long)v * 9 + k] = Hh[k] * ih;
+            }
+            __syncwarp();
         }
     }
 }

@@ -25,9 +25,18 @@ def _sym3(p):
 
 def estimateHomographies(prob):
     """linearcalibrate.estimateHomographies / estimateHomography (src/linearcalibrate.py:7-58) for all
-    views of a Problem: the device forms the point normalisations and the Gram matrix of the DLT system,
-    the homography is its eigenvector of the smallest eigenvalue (the reference: last right-singular
-    vector of the 2N x 9 matrix; same vector up to sign, removed by H /= H[2,2]).  Returns (M, 3, 3)."""
+    views of a Problem, entirely on the device (calib_dlt_homographies): point normalisations, the Gram
+    matrix of the DLT system, its eigenvector of the smallest eigenvalue by Jacobi rotations (the
+    reference: last right-singular vector of the 2N x 9 matrix; same vector up to sign, removed by
+    H /= H[2,2]) and the de-normalisation.  Returns (M, 3, 3)."""
+    H = np.zeros((prob.M, 9))
+    prob._check(prob._L.calib_dlt_homographies(prob._h, dptr(H)))
+    return H.reshape(prob.M, 3, 3)
+
+
+def estimateHomographiesHostEig(prob):
+    """The same with the 9 x 9 eigenvectors taken by LAPACK on the host from the device's Gram sums
+    (calib_dlt_gram): the cross-check of the device's Jacobi solver in the tests."""
     M = prob.M
     gram = np.zeros((M, 24))
     norm = np.zeros((M, 6))

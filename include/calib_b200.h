@@ -193,6 +193,11 @@ int calib_refine_homographies(calib_t* h, double* H_inout, int maxIters, double 
  * (R row-major, then t).  rows: M x 20 per-view sums: the upper triangle of D^T D (nd (nd+1) / 2,
  * row-major) then D^T Ddot (nd), nd = 5 | 4, zero padded; k solves (sum D^T D) k = sum D^T Ddot. */
 int calib_dlt_gram(calib_t* h, double* gram, double* norm);
+/* linearcalibrate.estimateHomographies, src/linearcalibrate.py:7-21, complete: the Gram sums above and,
+ * by the same warp, the eigenvector of the smallest eigenvalue of the 9 x 9 matrix (cyclic Jacobi
+ * rotations; the reference: last right-singular vector of the 2N x 9 matrix, :52-56), de-normalised and
+ * divided by H[2,2] (:57-58).  H: M x 9 row-major. */
+int calib_dlt_homographies(calib_t* h, double* H);
 int calib_distortion_rows(calib_t* h, const double* A, const double* W, double* rows);
 
 /* Multi-GPU, one process per GPU: views are sharded, every rank holds the L shared parameters

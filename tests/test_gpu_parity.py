@@ -476,6 +476,9 @@ def test_initial_estimate_vs_reference(golden, case):
     H0 = linearcalibrate.estimateHomographies(prob).reshape(-1, 9)
     ref = hg[case + "_H0"]
     assert (np.abs(H0 - ref) / np.maximum(np.abs(ref), 1e-3)).max() < 1e-7
+    # the device's Jacobi eigenvectors against LAPACK's on the same Gram sums
+    H1 = linearcalibrate.estimateHomographiesHostEig(prob).reshape(-1, 9)
+    assert (np.abs(H0 - H1) / np.maximum(np.abs(H1), 1e-3)).max() < 1e-8
     # distortion rows against the oracle at the oracle's own (A, W)
     A, Ws, k, Hs = lo.estimate_calibration_parameters(model, dets)
     kd = linearcalibrate.estimateDistortion(prob, A, Ws)

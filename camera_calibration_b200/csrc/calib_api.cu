@@ -27,16 +27,18 @@ using namespace calib;
 
 static thread_local std::string g_last_error;
 
+// Scratch buffers of one call: stream-ordered allocations from the device pool (which keeps what is
+// freed, pool_keep_memory), so a call costs no cudaMalloc / cudaFree.
 template <typename T>
-static cudaError_t dalloc(std::vector<void*>& pool, T** p, size_t count) {
+static cudaError_t dalloc(std::vector<void*>& pool, T** p, size_t count, cudaStream_t stream) {
     void* q = nullptr;
-    cudaError_t e = cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(T));
+    cudaError_t e = cudaMallocAsync(&q, std::max<size_t>(count, 1) * sizeof(T), stream);
     if (e == cudaSuccess) { pool.push_back(q); *p = (T*)q; }
     return e;
 }
 
-static void free_pool(std::vector<void*>& pool) {
-    for (void* p : pool) cudaFree(p);
+static void free_pool(std::vector<void*>& pool, cudaStream_t stream) {
+    for (void* p : pool) cudaFreeAsync(p, stream);
     pool.clear();
 }
 
@@ -1174,10 +1176,10 @@ int debug_point(calib_handle* h, const double* P, double* y, double* r, double* 
     const size_t N = (size_t)std::max<int64_t>(h->N, 1);
     double *dy = nullptr, *dr = nullptr, *dJc = nullptr, *dJv = nullptr;
     std::vector<void*> tmp;
-    if (y) CUDA_TRY(h, dalloc(tmp, &dy, 2 * N));
-    if (r) CUDA_TRY(h, dalloc(tmp, &dr, 2 * N));
-    if (Jc) CUDA_TRY(h, dalloc(tmp, &dJc, 2 * N * h->L));
-    if (Jv) CUDA_TRY(h, dalloc(tmp, &dJv, 12 * N));
+    if (y) CUDA_TRY(h, dalloc(tmp, &dy, 2 * N, h->stream));
+    if (r) CUDA_TRY(h, dalloc(tmp, &dr, 2 * N, h->stream));
+    if (Jc) CUDA_TRY(h, dalloc(tmp, &dJc, 2 * N * h->L, h->stream));
+    if (Jv) CUDA_TRY(h, dalloc(tmp, &dJv, 12 * N, h->stream));
     if (h->model == 0) launch_debug_point<0>(h, dy, dr, dJc, dJv);
     else launch_debug_point<1>(h, dy, dr, dJc, dJv);
     int rc = sync(h);
@@ -1186,7 +1188,7 @@ int debug_point(calib_handle* h, const double* P, double* y, double* r, double* 
     if (!rc && r) cudaMemcpy(r, dr, 2 * n * sizeof(double), cudaMemcpyDeviceToHost);
     if (!rc && Jc) cudaMemcpy(Jc, dJc, 2 * n * h->L * sizeof(double), cudaMemcpyDeviceToHost);
     if (!rc && Jv) cudaMemcpy(Jv, dJv, 12 * n * sizeof(double), cudaMemcpyDeviceToHost);
-    free_pool(tmp);
+    free_pool(tmp, h->stream);
     return rc;
 }
 
@@ -1249,10 +1251,10 @@ extern "C" int calib_eval_normal_equations(calib_t* h, const double* P, double* 
     const size_t M = (size_t)h->M;
     double *dA = nullptr, *dB = nullptr, *dD = nullptr, *dg = nullptr;
     std::vector<void*> tmp;
-    CUDA_TRY(h, dalloc(tmp, &dA, (size_t)L * L));
-    CUDA_TRY(h, dalloc(tmp, &dB, M * L * 6));
-    CUDA_TRY(h, dalloc(tmp, &dD, M * 36));
-    CUDA_TRY(h, dalloc(tmp, &dg, (size_t)h->K));
+    CUDA_TRY(h, dalloc(tmp, &dA, (size_t)L * L, h->stream));
+    CUDA_TRY(h, dalloc(tmp, &dB, M * L * 6, h->stream));
+    CUDA_TRY(h, dalloc(tmp, &dD, M * 36, h->stream));
+    CUDA_TRY(h, dalloc(tmp, &dg, (size_t)h->K, h->stream));
     const int nb = (int)((h->M + 127) / 128);
     if (h->model == 0) k_debug_unpack<0><<<nb, 128, 0, h->stream>>>(h->dev, dA, dB, dD, dg);
     else k_debug_unpack<1><<<nb, 128, 0, h->stream>>>(h->dev, dA, dB, dD, dg);
@@ -1264,7 +1266,7 @@ extern "C" int calib_eval_normal_equations(calib_t* h, const double* P, double* 
         cudaMemcpy(g, dg, (size_t)h->K * sizeof(double), cudaMemcpyDeviceToHost);
         cudaMemcpy(E, h->dev.red + kRedE, sizeof(double), cudaMemcpyDeviceToHost);
     }
-    free_pool(tmp);
+    free_pool(tmp, h->stream);
     return rc;
 }
 
@@ -1493,10 +1495,10 @@ extern "C" int calib_refine_homographies(calib_t* h, double* H_inout, int maxIte
     double *d_H = nullptr, *d_tr = nullptr;
     int* d_it = nullptr;
     int rc = [&]() -> int {
-        CUDA_TRY(h, dalloc(tmp, &d_offs, M + 1));
-        CUDA_TRY(h, dalloc(tmp, &d_H, M * 9));
-        CUDA_TRY(h, dalloc(tmp, &d_it, M));
-        if (trace) CUDA_TRY(h, dalloc(tmp, &d_tr, M * (size_t)maxIters * 4));
+        CUDA_TRY(h, dalloc(tmp, &d_offs, M + 1, h->stream));
+        CUDA_TRY(h, dalloc(tmp, &d_H, M * 9, h->stream));
+        CUDA_TRY(h, dalloc(tmp, &d_it, M, h->stream));
+        if (trace) CUDA_TRY(h, dalloc(tmp, &d_tr, M * (size_t)maxIters * 4, h->stream));
         static_assert(sizeof(long long) == sizeof(int64_t), "int64 layout");
         CUDA_TRY(h, cudaMemcpyAsync(d_offs, h->view_offsets.data(), (M + 1) * 8, cudaMemcpyHostToDevice, h->stream));
         CUDA_TRY(h, cudaMemcpyAsync(d_H, H_inout, M * 72, cudaMemcpyHostToDevice, h->stream));
@@ -1514,7 +1516,7 @@ extern "C" int calib_refine_homographies(calib_t* h, double* H_inout, int maxIte
         if (trace) CUDA_TRY(h, cudaMemcpyAsync(trace, d_tr, M * (size_t)maxIters * 32, cudaMemcpyDeviceToHost, h->stream));
         return sync(h);
     }();
-    free_pool(tmp);
+    free_pool(tmp, h->stream);
     return rc;
 }
 
@@ -1527,9 +1529,9 @@ int linear_call(calib_handle* h, int which, const double* A9, const double* W12,
     int rc = [&]() -> int {
         long long* d_offs = nullptr;
         double *d0 = nullptr, *d1 = nullptr, *dA = nullptr, *dW = nullptr;
-        CUDA_TRY(h, dalloc(tmp, &d_offs, M + 1));
-        CUDA_TRY(h, dalloc(tmp, &d0, M * n0));
-        if (n1) CUDA_TRY(h, dalloc(tmp, &d1, M * n1));
+        CUDA_TRY(h, dalloc(tmp, &d_offs, M + 1, h->stream));
+        CUDA_TRY(h, dalloc(tmp, &d0, M * n0, h->stream));
+        if (n1) CUDA_TRY(h, dalloc(tmp, &d1, M * n1, h->stream));
         CUDA_TRY(h, cudaMemcpyAsync(d_offs, h->view_offsets.data(), (M + 1) * 8, cudaMemcpyHostToDevice, h->stream));
         LinDev d;
         memset(&d, 0, sizeof d);
@@ -1539,14 +1541,14 @@ int linear_call(calib_handle* h, int which, const double* A9, const double* W12,
         if (which == 0 || which == 2) {
             if (which == 0) { d.gram = d0; d.norm = d1; }
             else {          // the homographies are what leaves the device; Gram sums and normalisations stay
-                CUDA_TRY(h, dalloc(tmp, &d.gram, M * kGramN));
-                CUDA_TRY(h, dalloc(tmp, &d.norm, M * kNormN));
+                CUDA_TRY(h, dalloc(tmp, &d.gram, M * kGramN, h->stream));
+                CUDA_TRY(h, dalloc(tmp, &d.norm, M * kNormN, h->stream));
                 d.Hdlt = d0;
             }
             k_dlt_gram<<<blocks, kBlockThreads, 0, h->stream>>>(d);
         } else {
-            CUDA_TRY(h, dalloc(tmp, &dA, 9));
-            CUDA_TRY(h, dalloc(tmp, &dW, M * 12));
+            CUDA_TRY(h, dalloc(tmp, &dA, 9, h->stream));
+            CUDA_TRY(h, dalloc(tmp, &dW, M * 12, h->stream));
             CUDA_TRY(h, cudaMemcpyAsync(dA, A9, 72, cudaMemcpyHostToDevice, h->stream));
             CUDA_TRY(h, cudaMemcpyAsync(dW, W12, M * 96, cudaMemcpyHostToDevice, h->stream));
             d.A = dA; d.W = dW; d.drows = d0;
@@ -1558,7 +1560,7 @@ int linear_call(calib_handle* h, int which, const double* A9, const double* W12,
         if (n1) CUDA_TRY(h, cudaMemcpyAsync(out1, d1, M * n1 * 8, cudaMemcpyDeviceToHost, h->stream));
         return sync(h);
     }();
-    free_pool(tmp);
+    free_pool(tmp, h->stream);
     return rc;
 }
 }  // namespace

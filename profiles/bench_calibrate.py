@@ -62,10 +62,12 @@ for _ in range(5):
     if best is None or sum(t.values()) < sum(best.values()):
         best = t
 A, k, sse, it = res
-t0 = time.perf_counter()
-with contextlib.redirect_stdout(io.StringIO()):
-    out = cal.calibrate(dets, 100)
-t_api = time.perf_counter() - t0
+t_api = 1e9
+for _ in range(4):      # the first call also sets up the library's page-locked staging (one-off)
+    t0 = time.perf_counter()
+    with contextlib.redirect_stdout(io.StringIO()):
+        out = cal.calibrate(dets, 100)
+    t_api = min(t_api, time.perf_counter() - t0)
 # the oracle's linear stage on a sample of views (exactly linear in views up to the two small SVDs)
 sub = dets[:min(cpu_views, M)]
 t0 = time.perf_counter()

@@ -32,75 +32,15 @@ __host__ __device__ inline int a_slot(int i, int j) {
     return S::kk(i - 5, j - 5);
 }
 
-// ---- reduced L x L system: Cholesky solve by one warp, trial shared parameters ------------------
+// ---- reduced L x L system: Cholesky solve by one warp ------------------------------------------
 // Lane i keeps row i of S in registers; the factorisation is right-looking (after column j every
 // lane updates the rest of its row), so the serial chain per column is one reciprocal square root,
-// one multiply and two shuffles.
+// one multiply and two shuffles.  The factor goes back to shared memory so that the back-substitution
+// reads L[j][i] instead of shuffling whole rows.  S: L x L row-major, then the right-hand side.
+// Returns dc[lane] for lane < L.
 struct LdCg { __device__ __forceinline__ double operator()(const double* p) const { return __ldcg(p); } };
 struct LdPlain { __device__ __forceinline__ double operator()(const double* p) const { return *p; } };
 
-// redA: the intrinsic-sweep slots (A and g_c), redW: W = sum Z^T Z (upper triangle) then w.
-// Returns dc[lane] for lane < L.
-template <int MODEL, class Ld>
-__device__ __forceinline__ double solve_reduced_core(const double* redA, const double* redW, double lam,
-                                                     int lane, Ld ld) {
-    using T = ModelTraits<MODEL>;
-    constexpr int L = T::L, ND = T::ND;
-    using SA = SlotsA<ND>;
-    const int i = lane < L ? lane : L - 1;       // idle lanes mirror the last row (no divergence)
-    double row[L];
-#pragma unroll
-    for (int j = 0; j < L; ++j) {
-        const int lo = i < j ? i : j, hi = i < j ? j : i;
-        const int sl = a_slot<ND>(lo, hi);
-        double a = sl >= 0 ? ld(redA + sl) : 0.0;
-        if (i == j) a = fma(lam, a, a);
-        row[j] = a - ld(redW + tri(L, lo, hi));
-    }
-    double rhs = ld(redA + SA::G + i) - ld(redW + L * (L + 1) / 2 + i);
-    double inv[L];
-#pragma unroll
-    for (int j = 0; j < L; ++j) {
-        const double dj = __shfl_sync(0xffffffffu, row[j], j);
-        const double id = rsqrt(dj);             // dj <= 0 or NaN poisons the step (rejected)
-        inv[j] = id;
-        const double lij = row[j] * id;          // column j of the factor (rows >= j meaningful)
-        row[j] = lij;
-#pragma unroll
-        for (int k = 0; k < L; ++k) {
-            if (k > j) {
-                const double lkj = __shfl_sync(0xffffffffu, lij, k);
-                row[k] = fma(-lij, lkj, row[k]);     // S[i][k] -= L[i][j] L[k][j]
-            }
-        }
-    }
-    // L y = s (column oriented): y_j = rhs_j / L_jj, then rhs_i -= L_ij y_j for i > j
-#pragma unroll
-    for (int j = 0; j < L; ++j) {
-        const double yj = __shfl_sync(0xffffffffu, rhs * inv[j], j);
-        if (i == j) rhs = yj;
-        else if (i > j) rhs = fma(-row[j], yj, rhs);
-    }
-    // L^T dc = y: dc_j = y_j / L_jj, then y_i -= L_ji dc_j for i < j (L_ji lives in lane j)
-#pragma unroll
-    for (int j = L - 1; j >= 0; --j) {
-        const double xj = __shfl_sync(0xffffffffu, rhs * inv[j], j);
-        double mine = 0.0;                       // L[j][i]: element i of lane j's row
-#pragma unroll
-        for (int k = 0; k < L; ++k) {
-            const double v = __shfl_sync(0xffffffffu, row[k], j);
-            if (k == i) mine = v;
-        }
-        if (i == j) rhs = xj;
-        else if (i < j) rhs = fma(-mine, xj, rhs);
-    }
-    return rhs;
-}
-
-// ---- the same solve for the large path, with everything that is not the serial chain taken off it ----
-// One warp: Cholesky solve of the dense system (same operations, same order as
-// solve_reduced_core); the factor goes back to shared memory so that the back-substitution reads
-// L[j][i] instead of shuffling whole rows.  Returns dc[lane] for lane < L.
 template <int L>
 __device__ __forceinline__ double solve_dense_core(double* S, int lane) {
     const int i = lane < L ? lane : L - 1;       // idle lanes mirror the last row (no divergence)

@@ -722,3 +722,31 @@ def test_many_handles_created_and_destroyed(golden):
     prob = _problem(gs[0])
     assert prob.lm_run(gs[0]["P0"], 30)[0] == first[0][0]
     prob.close()
+
+
+def test_reference_itest_cases_through_calibrate_camera():
+    """The three cases of the reference's integration test (tests/itest_main.py), through the same
+    entry point (main.calibrateCamera) and with the same assertions:
+    realistic radtan, 25x18 board, 15 views, no noise, maxIters 100 -> sse ~ 0 (7 places), A and k to
+    1e-9 of the ground truth, every board pose to atol 1 (:12-29); the 9x6 board with 0.1 px noise -> A
+    within 2.0, k within 0.05 (:31-52); fisheye, maxIters 10 -> runs and returns finite values (:54-79)."""
+    import contextlib
+    import io
+    out = io.StringIO()
+    c = synth.config("itest")
+    with contextlib.redirect_stdout(out):
+        sse, A, W, k = cc.calibrateCamera(c["dets"], "radtan", 100)
+    assert round(sse, 7) == 0.0
+    assert np.allclose(A, c["A"], atol=1e-9) and np.allclose(k, c["k"], atol=1e-9)
+    assert len(W) == len(c["poses"])
+    for Wc, Wt in zip(W, c["poses"]):
+        assert np.allclose(Wc, Wt, atol=1.0)
+    assert "iter 0: error=" in out.getvalue()          # Calibrator.calibrate prints (shouldPrint=True, :36-38)
+    c = synth.config("cfg1n")
+    with contextlib.redirect_stdout(io.StringIO()):
+        sse, A, W, k = cc.calibrateCamera(c["dets"], "radtan", 100)
+    assert np.allclose(A, c["A"], atol=2.0) and np.allclose(k, c["k"], atol=0.05)
+    c = synth.config("cfg2")
+    with contextlib.redirect_stdout(io.StringIO()):
+        sse, A, W, k = cc.calibrateCamera(c["dets"], "fisheye", 10)
+    assert np.isfinite(sse) and np.isfinite(A).all() and np.isfinite(np.asarray(k)).all() and len(k) == 4

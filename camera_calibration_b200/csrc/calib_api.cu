@@ -676,7 +676,10 @@ extern "C" void calib_destroy(calib_t* h) {
     }
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
-    park_graphs(h);       // destroyed by the next calib_create, under its upload
+    // The graphs are destroyed by the next calib_create, under its upload -- unless they hold NCCL nodes:
+    // ncclCommDestroy waits for every graph that captured its collectives, so those go first, now.
+    if (h->comm) drop_graph(h);
+    else park_graphs(h);
     if (h->comm && h->comm_owned && g_nccl.ok) g_nccl.CommDestroy(h->comm);
     for (auto& pe : h->prof_events) { cudaEventDestroy(pe.second.first); cudaEventDestroy(pe.second.second); }
     if (h->arena_part && h->stream) cudaFreeAsync(h->arena_part, h->stream);

@@ -27,7 +27,7 @@ def test_sharded_equals_single(case, scale, loop_mode, transport):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", "29541",
            os.path.join(ROOT, "tests", "mp", "sharded_worker.py"), case, str(scale), str(loop_mode), transport]
-    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
     lines = [ln for ln in res.stdout.splitlines() if ln.startswith("{")]
     assert res.returncode == 0 and lines, res.stdout[-2000:] + res.stderr[-6000:]
     out = json.loads(lines[-1])

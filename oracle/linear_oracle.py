@@ -44,6 +44,56 @@ def estimate_homography(Xa, Xb):
     return H / H[2, 2]
 
 
+def jacobi_smallest_eigenvector(G, max_sweeps=30, eps=1e-17):
+    """CPU restatement of the device's 9 x 9 symmetric eigen-solver (warp_jacobi9 in
+    camera_calibration_b200/csrc/calib_linear.cuh): cyclic Jacobi rotations in the same pivot order with
+    the same skip rule |a_pq| <= eps sqrt(|a_pp a_qq|) and the same rotation formulas; returns
+    (eigenvector of the smallest eigenvalue, its eigenvalue, sweeps used).  Test infrastructure: it pins
+    the convergence and accuracy of that scheme against LAPACK on the CPU."""
+    A = np.array(G, dtype=np.float64)
+    n = A.shape[0]
+    V = np.eye(n)
+    sweeps = 0
+    for sweeps in range(1, max_sweeps + 1):
+        rotated = False
+        for p in range(n - 1):
+            for q in range(p + 1, n):
+                apq, app, aqq = A[p, q], A[p, p], A[q, q]
+                if not abs(apq) > eps * np.sqrt(abs(app * aqq)):
+                    continue
+                rotated = True
+                theta = (aqq - app) / (2.0 * apq)
+                t = np.copysign(1.0, theta) / (abs(theta) + np.sqrt(theta * theta + 1.0))
+                c = 1.0 / np.sqrt(t * t + 1.0)
+                sn = t * c
+                vp, vq = V[:, p].copy(), V[:, q].copy()
+                V[:, p], V[:, q] = c * vp - sn * vq, sn * vp + c * vq
+                akp, akq = A[:, p].copy(), A[:, q].copy()
+                newp, newq = c * akp - sn * akq, sn * akp + c * akq
+                for k in range(n):
+                    if k != p and k != q:
+                        A[k, p] = A[p, k] = newp[k]
+                        A[k, q] = A[q, k] = newq[k]
+                A[p, p], A[q, q] = app - t * apq, aqq + t * apq
+                A[p, q] = A[q, p] = 0.0
+        if not rotated:
+            break
+    j = int(np.argmin(np.diag(A)))
+    return V[:, j], A[j, j], sweeps
+
+
+def estimate_homography_jacobi(Xa, Xb):
+    """estimate_homography with the eigenvector of M^T M taken by jacobi_smallest_eigenvector (what the
+    device does) instead of the last right-singular vector of M (what the reference does)."""
+    Na, Nb = normalization_matrix(Xa), normalization_matrix(Xb)
+    xa = Xa * Na[0, 0] + Na[:2, 2]
+    xb = Xb * Nb[0, 0] + Nb[:2, 2]
+    M = dlt_rows(xa, xb)
+    h, lam, sweeps = jacobi_smallest_eigenvector(M.T @ M)
+    H = np.linalg.inv(Na) @ h.reshape(3, 3) @ Nb
+    return H / H[2, 2], lam, sweeps
+
+
 def _vec(H, p, q):
     return np.stack([H[:, 0, p] * H[:, 0, q],
                      H[:, 0, p] * H[:, 1, q] + H[:, 1, p] * H[:, 0, q],

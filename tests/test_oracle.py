@@ -238,3 +238,32 @@ def test_device_atan_polynomial():
             continue
         worst = max(worst, float(abs((mp.mpf(got) - ref) / ref)))
     assert worst <= 3e-16, worst
+
+
+@pytest.mark.parametrize("case", ["cfg1", "cfg1n", "cfg2", "itest"])
+def test_jacobi_eigenvector_scheme_vs_lapack(golden, case):
+    """The device takes the DLT homography as the eigenvector of the smallest eigenvalue of M^T M by
+    cyclic Jacobi rotations (calib_linear.cuh: warp_jacobi9).  Its CPU restatement
+    (linear_oracle.jacobi_smallest_eigenvector: same pivot order, skip rule and rotation formulas) on
+    every view of the golden cases -- from noise-free ones without distortion residual (smallest eigenvalue
+    at rounding level) to the strongly distorted itest board -- converges in well under the 30-sweep cap and gives the reference's homography
+    (last right-singular vector of M) to 1e-7 relative, LAPACK's eigh on the same matrix to 1e-8."""
+    import linear_oracle as lo
+    hg = _hom_cases()
+    g = golden(case)
+    offs, mp, sp = g["view_offsets"], g["model_pts"], g["sensor_pts"]
+    ref = hg[case + "_H0"].reshape(-1, 9)
+    worst_sweeps = 0
+    for v in range(len(offs) - 1):
+        s, m = sp[offs[v]:offs[v + 1], :2], mp[offs[v]:offs[v + 1], :2]
+        H, lam, sweeps = lo.estimate_homography_jacobi(s, m)
+        worst_sweeps = max(worst_sweeps, sweeps)
+        assert (np.abs(H.ravel() - ref[v]) / np.maximum(np.abs(ref[v]), 1e-3)).max() < 1e-7
+        Na, Nb = lo.normalization_matrix(s), lo.normalization_matrix(m)
+        M = lo.dlt_rows(s * Na[0, 0] + Na[:2, 2], m * Nb[0, 0] + Nb[:2, 2])
+        w, vec = np.linalg.eigh(M.T @ M)
+        Hl = np.linalg.inv(Na) @ vec[:, 0].reshape(3, 3) @ Nb
+        Hl = (Hl / Hl[2, 2]).ravel()
+        assert (np.abs(H.ravel() - Hl) / np.maximum(np.abs(Hl), 1e-3)).max() < 1e-8
+        assert abs(lam - w[0]) <= 1e-12 * w[-1]
+    assert worst_sweeps <= 15

@@ -199,7 +199,7 @@ __device__ __forceinline__ void accum_BD(const PointOut<MODEL>& o, double (&acc)
 // PF: how many 32-point steps ahead the points are fetched inside a piece (1 or 2).  A sweep that is
 // bound by FP64 issue needs 1; the cost sweep has so little arithmetic per point that one step in
 // flight per warp leaves it waiting for L2 (16 warps x 1.3 KB per SM against ~1300 cycles).
-template <int NV, int PF, class Begin, class Body, class End>
+template <int NV, int PF, bool COUNTED = false, class Begin, class Body, class End>
 __device__ __forceinline__ void sweep_pieces(const Dev& d, const Piece* __restrict__ pieces, const WarpRec& rec,
                                              const ViewC* const (&views)[NV], ViewC (&sview)[NV], int lane,
                                              Begin begin, Body body, End end) {
@@ -231,11 +231,25 @@ __device__ __forceinline__ void sweep_pieces(const Dev& d, const Piece* __restri
         begin(cur, pi);
         if (lane >= cur.count && has_next && lane < nxt.count) load_point(d, (long long)nxt.start + lane, pn);
         if constexpr (PF == 1) {
+            if constexpr (COUNTED) {
+            // the same loop with a step count and a running index: the piece's start and count are not
+            // live inside it (register pressure: see profiles/README.md, static look at k_eval)
+            const int steps = cur.count > lane ? (cur.count - lane + 31) >> 5 : 0;
+            long long idx = (long long)cur.start + lane;
+            for (int sidx = 0; sidx < steps; ++sidx) {
+                const Pt p = pn;
+                idx += 32;
+                if (sidx + 1 < steps) load_point(d, idx, pn);
+                else if (has_next && lane < nxt.count) load_point(d, (long long)nxt.start + lane, pn);
+                body(p);
+            }
+            } else {
             for (int i = lane; i < cur.count; i += 32) {
                 const Pt p = pn;
                 if (i + 32 < cur.count) load_point(d, (long long)cur.start + i + 32, pn);
                 else if (has_next && lane < nxt.count) load_point(d, (long long)nxt.start + lane, pn);
                 body(p);
+            }
             }
         } else {
             Pt pn2 = pn;

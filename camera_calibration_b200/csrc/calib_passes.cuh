@@ -98,7 +98,10 @@ __global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
             [&](const PointOut<MODEL>& o) { accum_A<MODEL>(o, acc, e); },
             [&](const Piece&, int) {});
 #else
-        sweep<false, 1, 1, 1, CALIB_EVAL_PF>(d, d.ev_piece, rec, views, sview[warp], warp, nullptr, lane,
+#ifndef CALIB_EVAL_COUNTED2
+#define CALIB_EVAL_COUNTED2 1   // sweep 2 with the counted loop of sweep_pieces (no spill loads inside it)
+#endif
+        sweep_pieces<1, CALIB_EVAL_PF, CALIB_EVAL_COUNTED2 != 0>(d, d.ev_piece, rec, views, sview[warp], lane,
             [&](const Piece&, int) {},
             [&](const Pt& p) {
                 PointOut<MODEL> o;

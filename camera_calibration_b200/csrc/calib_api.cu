@@ -18,7 +18,7 @@
 #include <vector>
 
 #include "../../include/calib_b200.h"
-#include "calib_solve.cuh"
+#include "calib_persistent.cuh"
 #include "calib_batch.cuh"
 #include "calib_homography.cuh"
 #include "calib_linear.cuh"
@@ -69,7 +69,8 @@ struct calib_handle {
     cudaStream_t stream = nullptr;
     cudaGraphExec_t graph = nullptr;       // one iteration (host-driven loop)
     cudaGraphExec_t loop_graph = nullptr;  // WHILE node around the iteration (device-driven loop)
-    int loop_mode = 0;                     // 0 auto, 1 host-driven, 2 device WHILE graph
+    int loop_mode = 0;                     // 0 auto, 1 host-driven, 2 device WHILE graph, 3 persistent kernel
+    int persist_blocks = 0;                // co-resident blocks of the persistent kernel on this device (0: not asked yet)
     int cost_tma = -1;                     // -1 auto (by size), 0 plain loads, 1 bulk-copy ring
     LmState* h_state = nullptr;   // pinned
     double* h_pinned = nullptr;   // pinned scratch (kRedN + 8 doubles)
@@ -160,7 +161,9 @@ struct Arena {
 };
 
 void pool_keep_memory(int device) {
+    static std::mutex mu;
     static bool done[64] = {false};
+    std::lock_guard<std::mutex> lk(mu);
     if (device < 0 || device >= 64 || done[device]) return;
     cudaMemPool_t pool;
     if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
@@ -385,6 +388,7 @@ static int ensure_trace(calib_handle* h, int iters) {
 }
 
 namespace {
+bool cost_uses_tma(const calib_handle* h);
 int build_loop_graph(calib_handle* h);
 void apply_transport(calib_handle* h);
 std::mutex g_default_mu;
@@ -519,6 +523,23 @@ cudaError_t upload_views_join(int device, cudaStream_t stream, int n_streams) {
 
 }  // namespace
 
+// Per-device function attributes (cudaFuncSetAttribute applies to the CURRENT device only): the
+// per-warp rings of the cost pass exceed the 48 KB default.  Done once per device, under a lock.
+static cudaError_t device_func_attributes(int device) {
+    static std::mutex mu;
+    static bool done[64] = {false};
+    std::lock_guard<std::mutex> lk(mu);
+    if (device >= 0 && device < 64 && done[device]) return cudaSuccess;
+    cudaError_t e = cudaSuccess;
+    auto set = [&](auto kern) {
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCostDynSmem);
+    };
+    set(k_cost<0, false, true>); set(k_cost<0, true, true>); set(k_cost<1, false, true>); set(k_cost<1, true, true>);
+    set(k_lm_persistent<0, true, 1>); set(k_lm_persistent<1, true, 1>);
+    if (e == cudaSuccess && device >= 0 && device < 64) done[device] = true;
+    return e;
+}
+
 static int create_impl(calib_t** out, int model, int64_t M, const int64_t* view_offsets, const double* model_pts,
                        const double* sensor_pts, const double* const* vmodel, const double* const* vsensor, int device_id) {
     if (!out) return fail(nullptr, CALIB_E_ARG, "calib_create: out is NULL");
@@ -551,16 +572,7 @@ static int create_impl(calib_t** out, int model, int64_t M, const int64_t* view_
 #define TRY_(call) do { int rc__ = [&]() -> int { CUDA_TRY(h, call); return 0; }(); if (rc__) { g_last_error = h->err; return bail(rc__); } } while (0)
     TRY_(cudaSetDevice(device_id));
     pool_keep_memory(device_id);
-    {   // the per-warp rings of the cost pass exceed the 48 KB default
-        static bool once = false;
-        if (!once) {
-            cudaFuncSetAttribute(k_cost<0, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCostDynSmem);
-            cudaFuncSetAttribute(k_cost<0, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCostDynSmem);
-            cudaFuncSetAttribute(k_cost<1, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCostDynSmem);
-            cudaFuncSetAttribute(k_cost<1, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCostDynSmem);
-            once = true;
-        }
-    }
+    TRY_(device_func_attributes(device_id));
     TRY_(cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, device_id));
     { int rc = ctx_acquire(h); if (rc) { g_last_error = h->err; return bail(rc); } }
     Dev& d = h->dev;
@@ -574,7 +586,7 @@ static int create_impl(calib_t** out, int model, int64_t M, const int64_t* view_
         const size_t o_et = a.reserve<double>(8), o_delta = a.reserve<double>((size_t)h->K);
         const size_t o_dcs = a.reserve<double>(kJMax * 16), o_redA = a.reserve<double>(kRedW0);
 #ifdef CALIB_STAMPS
-        const size_t o_stamps = a.reserve<unsigned long long>((size_t)4 * kStampBlocks * 8);
+        const size_t o_stamps = a.reserve<unsigned long long>(kStampWords);
 #endif
         const size_t o_st = a.reserve<LmState>(1);
         constexpr int kTraceIters = 256;
@@ -628,9 +640,8 @@ static int create_impl(calib_t** out, int model, int64_t M, const int64_t* view_
             apply_transport(h);
         }
     }
-    // the default loop graph is built here, on the host, while the detections are still crossing PCIe
-    // (a setting that changes the iteration drops it and lm_run rebuilds it)
-    if (build_loop_graph(h) != CALIB_OK) { cudaGetLastError(); drop_graph(h); }
+    // (the default loop is the persistent kernel: no graph to build; loop modes 1 and 2 build theirs on
+    // first use)
     empty_trash(device_id, 0);      // graphs of destroyed handles: torn down while the detections cross PCIe
     if (uploader.joinable() || upload_inline) {
         if (uploader.joinable()) uploader.join();
@@ -704,7 +715,7 @@ extern "C" int calib_set_segment(calib_t* h, int points_per_task) {
 
 extern "C" int calib_set_loop_mode(calib_t* h, int mode) {
     if (!h) return fail(nullptr, CALIB_E_ARG, "NULL handle");
-    if (mode < 0 || mode > 2) return fail(h, CALIB_E_ARG, "calib_set_loop_mode: 0 auto, 1 host, 2 device");
+    if (mode < 0 || mode > 3) return fail(h, CALIB_E_ARG, "calib_set_loop_mode: 0 auto, 1 host, 2 device graph, 3 persistent kernel");
     h->loop_mode = mode;
     return CALIB_OK;
 }
@@ -860,8 +871,7 @@ void enqueue_cost(calib_handle* h, Launcher& ln, int fuse_accept) {
     const Dev& d = h->dev;
     cudaEvent_t a, b;
     ln.begin(&a, &b);
-    // bulk-copy ring when the detections cannot stay in L2 between the sweeps, plain loads otherwise
-    const bool tma = h->cost_tma >= 0 ? h->cost_tma != 0 : (size_t)h->N * 40 > ((size_t)96 << 20);
+    const bool tma = cost_uses_tma(h);
     if (tma) {
         if (d.use_cond) launch_iter(h, k_cost<MODEL, true, true>, d.co_blocks, kBlockThreads, kCostDynSmem, d, fuse_accept);
         else launch_iter(h, k_cost<MODEL, false, true>, d.co_blocks, kBlockThreads, kCostDynSmem, d, fuse_accept);
@@ -1020,6 +1030,45 @@ int check_handle(calib_handle* h) {
 
 }  // namespace
 
+// ---- the persistent kernel (calib_persistent.cuh) ---------------------------------------------------
+namespace {
+bool cost_uses_tma(const calib_handle* h) {
+    // bulk-copy ring when the detections cannot stay in L2 between the sweeps, plain loads otherwise
+    return h->cost_tma >= 0 ? h->cost_tma != 0 : (size_t)h->N * 40 > ((size_t)96 << 20);
+}
+
+template <int MODEL, bool TMA, int PF>
+int launch_persistent_t(calib_handle* h) {
+    auto kern = k_lm_persistent<MODEL, TMA, PF>;
+    const size_t smem = TMA ? kCostDynSmem : 0;
+    if (h->persist_blocks <= 0) {
+        int per_sm = 0;
+        CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kBlockThreads, smem));
+        if (per_sm < 1) return fail(h, CALIB_E_CUDA, "persistent kernel: no block fits an SM");
+        h->persist_blocks = h->n_sm;      // one block per SM: the evaluation sweep is sized for that
+    }
+    const Dev& d = h->dev;
+    // as many blocks as the widest phase can use, at most one per SM (all must be co-resident)
+    int want = std::max(std::max(d.ev_blocks, d.co_blocks), d.sc_groups * (int)kJMax);
+    want = std::max(1, std::min(want, h->persist_blocks));
+    void* args[] = {(void*)&h->dev};
+    CUDA_TRY(h, cudaLaunchCooperativeKernel((const void*)kern, dim3((unsigned)want), dim3(kBlockThreads), args, smem, h->stream));
+    return CALIB_OK;
+}
+
+int launch_persistent(calib_handle* h) {
+    static const int pf = [] { const char* e = getenv("CALIB_PERSIST_PF"); return e ? atoi(e) : 1; }();
+    const bool tma = cost_uses_tma(h);
+    h->dev.use_cond = 0;
+    if (h->model == 0) {
+        if (tma) return launch_persistent_t<0, true, 1>(h);
+        return pf == 2 ? launch_persistent_t<0, false, 2>(h) : launch_persistent_t<0, false, 1>(h);
+    }
+    if (tma) return launch_persistent_t<1, true, 1>(h);
+    return pf == 2 ? launch_persistent_t<1, false, 2>(h) : launch_persistent_t<1, false, 1>(h);
+}
+}  // namespace
+
 // ---- LM loop ------------------------------------------------------------------------------------
 extern "C" int calib_upload_params(calib_t* h, const double* P) {
     RC(check_handle(h));
@@ -1058,8 +1107,14 @@ extern "C" int calib_lm_run_resident(calib_t* h, int maxIters, double lam0, doub
     if (h->loop_mode == 2 && nccl_active(h))
         return fail(h, CALIB_E_STATE, "loop mode 2: a WHILE-node body cannot hold NCCL nodes (cudaGraphInstantiate rejects "
                                       "them); use the peer-memory transport (calib_peer_attach) or loop mode 1");
-    const bool device_loop = !prof && (h->loop_mode == 2 || (h->loop_mode == 0 && !nccl_active(h)));
-    if (!prof) {
+    if (h->loop_mode == 3 && nccl_active(h))
+        return fail(h, CALIB_E_STATE, "loop mode 3: the persistent kernel sums over the ranks through peer memory "
+                                      "(calib_peer_attach); NCCL all-reduces need loop mode 1");
+    // default: the persistent kernel (one cooperative launch per refinement) on one GPU and with the
+    // peer-memory transport; iteration graphs driven by the host with NCCL
+    const bool persistent = !prof && (h->loop_mode == 3 || (h->loop_mode == 0 && !nccl_active(h)));
+    const bool device_loop = !prof && h->loop_mode == 2;
+    if (!prof && !persistent) {
         int rc = device_loop ? build_loop_graph(h) : build_graph(h);
         if (rc && h->pdl) {          // a driver that rejects programmatic edges here: plain edges
             h->pdl = 0;
@@ -1074,11 +1129,19 @@ extern "C" int calib_lm_run_resident(calib_t* h, int maxIters, double lam0, doub
     for (int i = 0; i < 5; ++i) { h->ktime[i] = 0; h->kcount[i] = 0; }
     RC(push_state(h, lam0, lam_min, lam_max, err_min, maxIters, h->ladder));
     CUDA_TRY(h, cudaEventRecord(h->ev0, h->stream));
-    RC(make_views(h, 1));
     Launcher ln{h, prof};
-    ln.count = 1;
     const int kpi = kernels_per_iteration(h);
-    if (device_loop) {
+    if (persistent) {
+        RC(launch_persistent(h));
+        ln.count = 1;
+        CUDA_TRY(h, cudaMemcpyAsync(h->h_state, h->dev.st, sizeof(LmState), cudaMemcpyDeviceToHost, h->stream));
+        CUDA_TRY(h, cudaEventRecord(h->ev1, h->stream));
+        RC(sync(h));
+        if (h->h_state->bar_abort)
+            return fail(h, CALIB_E_CUDA, "persistent kernel: a block waited too long at a grid barrier (grid not co-resident?)");
+    } else if (device_loop) {
+        RC(make_views(h, 1));
+        ln.count = 1;
         CUDA_TRY(h, cudaGraphLaunch(h->loop_graph, h->stream));
         CUDA_TRY(h, cudaMemcpyAsync(h->h_state, h->dev.st, sizeof(LmState), cudaMemcpyDeviceToHost, h->stream));
         CUDA_TRY(h, cudaEventRecord(h->ev1, h->stream));
@@ -1086,6 +1149,8 @@ extern "C" int calib_lm_run_resident(calib_t* h, int maxIters, double lam0, doub
         // skipped evaluations (after a rejected step) still launch and return at once
         ln.count += (int64_t)kpi * h->h_state->n_pass;
     } else {
+        RC(make_views(h, 1));
+        ln.count = 1;
         int enq = 0;
         int batch = 2;   // iterations enqueued between two looks at the device state
         while (enq < maxIters) {
@@ -1716,8 +1781,6 @@ extern "C" int calib_batch_create(calib_batch_t** out, int model, int64_t n_prob
     }
     d.prob_view = pv; d.view_off = vo;
     d.X = soa; d.Y = soa + n; d.Z = soa + 2 * n; d.U = soa + 3 * n; d.V = soa + 4 * n;
-    TRYB_(cudaFuncSetAttribute(k_batch_lm<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_bytes));
-    TRYB_(cudaFuncSetAttribute(k_batch_lm<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_bytes));
     TRYB_(cudaStreamSynchronize(h->stream));
 #undef TRYB_
     *out = h;
@@ -1747,6 +1810,9 @@ extern "C" int calib_batch_lm_run(calib_batch_t* h, double* P_inout, int maxIter
         d.trace = h->trace_dev;
     }
     BATCH_TRY(h, cudaMemcpyAsync(d.P, P_inout, (size_t)h->total_params * 8, cudaMemcpyHostToDevice, h->stream));
+    // per launch and device: another live batch handle may need a different size
+    if (h->model == 0) BATCH_TRY(h, cudaFuncSetAttribute(k_batch_lm<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_bytes));
+    else BATCH_TRY(h, cudaFuncSetAttribute(k_batch_lm<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_bytes));
     BATCH_TRY(h, cudaEventRecord(h->ev0, h->stream));
     if (h->model == 0) k_batch_lm<0><<<(int)h->n_problems, kBatchThreads, h->smem_bytes, h->stream>>>(d);
     else k_batch_lm<1><<<(int)h->n_problems, kBatchThreads, h->smem_bytes, h->stream>>>(d);
@@ -1767,6 +1833,14 @@ extern "C" int calib_batch_lm_run(calib_batch_t* h, double* P_inout, int maxIter
 }
 
 #ifdef CALIB_STAMPS
+// latency-study builds only: the persistent kernel's stamps of the last run, [2][kPStampPasses][kPStampSlots]
+extern "C" int calib_debug_pstamps(calib_t* h, unsigned long long* out) {
+    RC(check_handle(h));
+    CUDA_TRY(h, cudaMemcpy(out, h->dev.stamps + (size_t)4 * kStampBlocks * 8, (size_t)2 * kPStampPasses * kPStampSlots * 8,
+                           cudaMemcpyDeviceToHost));
+    CUDA_TRY(h, cudaMemset(h->dev.stamps + (size_t)4 * kStampBlocks * 8, 0, (size_t)2 * kPStampPasses * kPStampSlots * 8));
+    return CALIB_OK;
+}
 // latency-study builds only (not in the header): one pass at P, then the globaltimer stamps
 extern "C" int calib_debug_stamps(calib_t* h, const double* P, double lam, unsigned long long* out) {
     RC(check_handle(h));

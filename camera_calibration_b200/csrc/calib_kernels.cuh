@@ -55,6 +55,8 @@ struct LmState {
     int n_pass;            // passes (one k_schur/k_backsub/k_cost each) so far
     unsigned int cnt_schur, cnt_cost, cnt_eval, pad1;
     long long n_eval;   // Jacobian evaluations actually executed
+    unsigned int bar_count;   // persistent kernel: arrivals at its grid barriers so far (calib_persistent.cuh)
+    int bar_abort;            // persistent kernel: a block gave up waiting at a barrier
 };
 
 struct Dev {  // everything the kernels need; passed by value
@@ -113,13 +115,33 @@ constexpr int kStampBlocks = 1280;
         if (threadIdx.x == 0 && blockIdx.x < kStampBlocks)                                             \
             (d).stamps[((kern) * kStampBlocks + blockIdx.x) * 8 + (slot)] = global_timer_ns();        \
     } while (0)
+// the persistent kernel: [first / last block][pass][slot] after the per-kernel stamps
+constexpr int kPStampPasses = 128, kPStampSlots = 16;
+constexpr size_t kStampWords = (size_t)4 * kStampBlocks * 8 + (size_t)2 * kPStampPasses * kPStampSlots;
+#define PSTAMP(d, pass, slot)                                                                              \
+    do {                                                                                                   \
+        if (tid_now() == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1) && (pass) < kPStampPasses)  \
+            (d).stamps[(size_t)4 * kStampBlocks * 8 +                                                      \
+                       ((size_t)(blockIdx.x == 0 ? 0 : 1) * kPStampPasses + (pass)) * kPStampSlots + (slot)] = global_timer_ns(); \
+    } while (0)
 #else
 #define STAMP(d, kern, slot) do {} while (0)
+#define PSTAMP(d, pass, slot) do {} while (0)
 #endif
 
 // Programmatic dependent launch (see launch_iter in calib_api.cu): no-ops without the launch attribute.
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+// threadIdx.x through a volatile asm: the phase functions of the iteration take their thread indices
+// this way so that, inlined one after the other into the persistent kernel, nothing derived from them
+// is kept alive (hoisted, common-subexpression'd) from one phase across the sweeps of another -- the
+// evaluation sweeps run at the 255-register limit and every such value became a spill inside them.
+__device__ __forceinline__ int tid_now() {
+    int t;
+    asm volatile("mov.u32 %0, %%tid.x;" : "=r"(t));
+    return t;
+}
 
 struct Pt { double X, Y, Z, U, V; };
 

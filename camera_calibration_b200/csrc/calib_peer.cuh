@@ -5,9 +5,12 @@
 // ladder) and the trial costs.  A library collective costs a launch (plus a 1-thread kernel to consume it) per exchange and
 // keeps the WHILE-graph loop off the table; here the last thread block of k_schur / k_cost does it:
 //   push   thread t stores value t of its rank's contribution into a slot of EVERY peer's inbox,
-//          through the NVLink mapping of the peer's memory, as ONE 16-byte store
-//          {low word, seq, high word, seq}: the data carry their own flag (each 8-byte half is
-//          written atomically), so there is no fence and no separate flag round trip;
+//          through the NVLink mapping of the peer's memory, as ONE 16-byte store of two 64-bit
+//          elements {seq:low word, seq:high word}: the data carry their own flag.  A vector access
+//          is a set of scalar accesses of its element type under the PTX memory model, and an
+//          aligned 64-bit scalar is single-copy atomic -- so each half arrives with ITS sequence
+//          number or not at all, and there is no fence and no separate flag round trip (a .v4.u32
+//          store, the first version, only promised that per 32-bit word);
 //   wait   thread t polls element t of every peer's slot in its LOCAL inbox until both sequence
 //          words match (a first version with fence.sys + a release flag cost 5-6 us per exchange);
 //   sum    in RANK ORDER (its own contribution from shared memory), so all ranks hold
@@ -34,15 +37,12 @@ struct PeerDev {
     unsigned int* seq;                        // local, kPeerChannels counters (exchanges done so far)
 };
 
-__device__ __forceinline__ void st_volatile_v4(uint4* p, const uint4& v) {
-    asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
-                 : "memory");
+// one inbox element: two 64-bit halves, each {sequence number : 32 bits of the double}
+__device__ __forceinline__ void st_volatile_v2(uint4* p, unsigned long long lo, unsigned long long hi) {
+    asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(lo), "l"(hi) : "memory");
 }
-__device__ __forceinline__ uint4 ld_volatile_v4(const uint4* p) {
-    uint4 v;
-    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p)
-                 : "memory");
-    return v;
+__device__ __forceinline__ void ld_volatile_v2(const uint4* p, unsigned long long& lo, unsigned long long& hi) {
+    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(lo), "=l"(hi) : "l"(p) : "memory");
 }
 __device__ __forceinline__ unsigned long long global_timer_ns() {
     unsigned long long t;
@@ -66,10 +66,11 @@ __device__ __forceinline__ bool peer_allreduce(const PeerDev& pc, int ch, double
     for (int e = tid; e < n; e += (int)blockDim.x) {
         const double mine = val[e];
         const unsigned long long bits = (unsigned long long)__double_as_longlong(mine);
-        const uint4 pk = make_uint4((unsigned)bits, seq, (unsigned)(bits >> 32), seq);
+        const unsigned long long tag = (unsigned long long)seq << 32;
+        const unsigned long long lo = tag | (bits & 0xffffffffull), hi = tag | (bits >> 32);
         const size_t off = peer_slot_off(ch, par, pc.rank) + e;
         for (int p = 0; p < pc.nranks; ++p)
-            if (p != pc.rank) st_volatile_v4(pc.box[p] + off, pk);
+            if (p != pc.rank) st_volatile_v2(pc.box[p] + off, lo, hi);
     }
     for (int e = tid; e < n; e += (int)blockDim.x) {
         const double mine = val[e];
@@ -78,16 +79,17 @@ __device__ __forceinline__ bool peer_allreduce(const PeerDev& pc, int ch, double
             double v = mine;
             if (r != pc.rank) {
                 const uint4* src = pc.box[pc.rank] + peer_slot_off(ch, par, r) + e;
-                uint4 g = ld_volatile_v4(src);
-                if (g.y != seq || g.w != seq) {
+                unsigned long long lo, hi;
+                ld_volatile_v2(src, lo, hi);
+                if ((unsigned)(lo >> 32) != seq || (unsigned)(hi >> 32) != seq) {
                     const unsigned long long t0 = global_timer_ns();
                     unsigned spins = 0;
                     do {
-                        g = ld_volatile_v4(src);
+                        ld_volatile_v2(src, lo, hi);
                         if ((++spins & 1023u) == 0 && global_timer_ns() - t0 > kPeerTimeoutNs) { *s_flag = 0; break; }
-                    } while (g.y != seq || g.w != seq);
+                    } while ((unsigned)(lo >> 32) != seq || (unsigned)(hi >> 32) != seq);
                 }
-                v = __longlong_as_double((long long)(((unsigned long long)g.z << 32) | g.x));
+                v = __longlong_as_double((long long)((hi << 32) | (lo & 0xffffffffull)));
             }
             s = __dadd_rn(s, v);
         }

@@ -92,14 +92,13 @@ __device__ __forceinline__ double solve_dense_core(double* S, int lane) {
 // the current cost IS the trial cost of the last accepted step, as in the reference where both
 // numbers come from one function (calibrate.py:155-156).
 template <int MODEL, class Ld>
-__device__ __forceinline__ void solve_candidates(const Dev& d, const double* red, double* dense, int J, Ld ld) {
+__device__ __forceinline__ void solve_candidates(const Dev& d, const double* red, double* dense, const PassCtx& c, Ld ld) {
     using T = ModelTraits<MODEL>;
     constexpr int L = T::L, ND = T::ND, NE = L * L + L;
     using SA = SlotsA<ND>;
-    LmState* st = d.st;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const double lam0 = st->lam;
-    const int cur = st->cur, iter = st->iter;
+    const int tid = tid_now(), lane = tid & 31, warp = tid >> 5;
+    const double lam0 = c.lam;
+    const int cur = c.cur, J = c.J;
     double pcur = 0.0;
     if (warp < J && lane < L) pcur = d.Pbuf[(long long)cur * d.K + lane];
     // dense S = A + lam diag(A) - W (L x L, row-major), then s = g_c - w (L), per candidate; red may be
@@ -112,11 +111,11 @@ __device__ __forceinline__ void solve_candidates(const Dev& d, const double* red
         const double* redW = red + red_w(j);
         double out;
         if (el < L * L) {
-            const int i = el / L, c = el - i * L;
-            const int lo = i < c ? i : c, hi = i < c ? c : i;
+            const int i = el / L, cc = el - i * L;
+            const int lo = i < cc ? i : cc, hi = i < cc ? cc : i;
             const int sl = a_slot<ND>(lo, hi);
             double v = sl >= 0 ? ld(redA + sl) : 0.0;
-            if (i == c) v = fma(lam, v, v);
+            if (i == cc) v = fma(lam, v, v);
             out = v - ld(redW + tri(L, lo, hi));
         } else {
             const int i = el - L * L;
@@ -132,140 +131,131 @@ __device__ __forceinline__ void solve_candidates(const Dev& d, const double* red
             d.dcs[warp * 16 + lane] = dc;
             d.Pbuf[(long long)trial_buf(cur, warp) * d.K + lane] = pcur + dc;
         }
-        if (warp == 0 && lane == 0 && iter == 0) st->E_cur = ld(red + kRedE);
     }
 }
 
 // ---- per-view Schur stage -------------------------------------------------------------------------
-// Grid = sc_groups x kJMax blocks: block (g, j) works for candidate j of the damping ladder (and
-// leaves at once when the pass has fewer candidates) on views 8 g + warp + k * 8 sc_groups, so the
-// views and the summation order of a candidate do not depend on how many candidates the pass has.
+template <int MODEL> struct SchurSmem {
+    static constexpr int L = ModelTraits<MODEL>::L;
+    double sv[kBlockWarps][kNBD];          // the view's summed piece rows; reused for sums
+    double sz[kBlockWarps][(L + 1) * 6];   // Z = L^-1 [B^T | g_v], column-major by c
+    double sl[kBlockWarps][24];            // packed lower factor of the view block
+    double sga[kBlockWarps][kNA], sge[kBlockWarps];
+    double sred[kRedN];                    // the reduced system in the layout of red[]
+    double sdense[kJMax * (L * L + L)];    // its dense form, per candidate
+    int s_last;
+};
+
+// Block (grp, cand) of the per-view stage: candidate `cand` of the damping ladder on views
+// 8 grp + warp + k * 8 sc_groups, so the views and the summation order of a candidate do not depend on
+// how many candidates the pass has.  lam0: damping of candidate 0.  Writes vtab and row (cand, grp) of
+// partW.  Called by all threads of a block; no barrier at entry, none after its last shared read.
 template <int MODEL>
-__global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) {
+__device__ __forceinline__ void schur_views_block(const Dev& d, SchurSmem<MODEL>& sm, int cand, int grp, double lam0) {
     using T = ModelTraits<MODEL>;
     constexpr int L = T::L, NZ = L + 1, NT = L * (L + 1) / 2, NW = NT + L;
     using S = SlotsBD<L>;
-    pdl_trigger();
-    pdl_wait();
-    LmState* st = d.st;
-    if (st->done) return;
-    __shared__ double sv[kBlockWarps][kNBD];       // the view's summed piece rows; reused for sums
-    __shared__ double sz[kBlockWarps][NZ * 6];     // Z = L^-1 [B^T | g_v], column-major by c
-    __shared__ double sl[kBlockWarps][24];         // packed lower factor of the view block
-    __shared__ double sga[kBlockWarps][kNA], sge[kBlockWarps];
-    __shared__ double sred[kRedN];                 // the reduced system in the layout of red[]
-    __shared__ double sdense[kJMax * (L * L + L)];  // its dense form, per candidate
-    __shared__ int s_last;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = tid_now(), lane = tid & 31, warp = tid >> 5;
     const int nvb = d.sc_groups;
-    const int J = st->J;
-    const int cand = blockIdx.x / nvb, grp = blockIdx.x - cand * nvb;
-    STAMP(d, 1, 0);
-    if (cand < J) {
-        // which entries of W this lane accumulates: e = lane + 32 k  ->  (p, c), c in [p, L]
-        int ep[3], ec[3];
+    // which entries of W this lane accumulates: e = lane + 32 k  ->  (p, c), c in [p, L]
+    int ep[3], ec[3];
 #pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            int e = lane + 32 * k;
-            ep[k] = -1; ec[k] = 0;
-            if (e < NT) {
-                int p = 0;
-                while (e >= L - p) { e -= L - p; ++p; }
-                ep[k] = p; ec[k] = p + e;
-            } else if (e < NW) {
-                ep[k] = e - NT; ec[k] = L;
-            }
+    for (int k = 0; k < 3; ++k) {
+        int e = lane + 32 * k;
+        ep[k] = -1; ec[k] = 0;
+        if (e < NT) {
+            int p = 0;
+            while (e >= L - p) { e -= L - p; ++p; }
+            ep[k] = p; ec[k] = p + e;
+        } else if (e < NW) {
+            ep[k] = e - NT; ec[k] = L;
         }
-        double wacc[3] = {0.0, 0.0, 0.0};
-        double lam = st->lam;
-        for (int k = 0; k < cand; ++k) lam = lam * 10.0;
-        double* vtab = d.vtab + (long long)cand * d.M * kVtab;
-        for (int v = grp * kBlockWarps + warp; v < d.M; v += nvb * kBlockWarps) {
-            const int r0 = d.view_piece[v], r1 = d.view_piece[v + 1];
-            double s0 = 0.0, s1 = 0.0, s2 = 0.0;
-            for (int r = r0; r < r1; ++r) {
-                const double* row = d.partBD + (long long)r * kNBD;
-                s0 += __ldcg(row + lane); s1 += __ldcg(row + lane + 32); s2 += __ldcg(row + lane + 64);
+    }
+    double wacc[3] = {0.0, 0.0, 0.0};
+    double lam = lam0;
+    for (int k = 0; k < cand; ++k) lam = lam * 10.0;
+    double* vtab = d.vtab + (long long)cand * d.M * kVtab;
+    for (int v = grp * kBlockWarps + warp; v < d.M; v += nvb * kBlockWarps) {
+        const int r0 = d.view_piece[v], r1 = d.view_piece[v + 1];
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0;
+        for (int r = r0; r < r1; ++r) {
+            const double* row = d.partBD + (long long)r * kNBD;
+            s0 += __ldcg(row + lane); s1 += __ldcg(row + lane + 32); s2 += __ldcg(row + lane + 64);
+        }
+        __syncwarp();
+        STAMP(d, 1, 1);
+        sm.sv[warp][lane] = s0; sm.sv[warp][lane + 32] = s1; sm.sv[warp][lane + 64] = s2;
+        __syncwarp();
+        // D' = D + lam diag(D), lower Cholesky, every lane redundantly (registers)
+        double Lc[36];
+#pragma unroll
+        for (int a = 0; a < 6; ++a)
+#pragma unroll
+            for (int b = a; b < 6; ++b) {
+                const double s = sm.sv[warp][S::dd(a, b)];
+                Lc[b * 6 + a] = (a == b) ? fma(lam, s, s) : s;
             }
-            __syncwarp();
-            STAMP(d, 1, 1);
-            sv[warp][lane] = s0; sv[warp][lane + 32] = s1; sv[warp][lane + 64] = s2;
-            __syncwarp();
-            // D' = D + lam diag(D), lower Cholesky, every lane redundantly (registers)
-            double Lc[36];
+        double id[6];
+        chol_inplace<6>(Lc, id);
+        double* vt = vtab + (long long)v * kVtab;
+        if (lane == 0) {
 #pragma unroll
             for (int a = 0; a < 6; ++a)
 #pragma unroll
-                for (int b = a; b < 6; ++b) {
-                    const double s = sv[warp][S::dd(a, b)];
-                    Lc[b * 6 + a] = (a == b) ? fma(lam, s, s) : s;
-                }
-            double id[6];
-            chol_inplace<6>(Lc, id);
-            double* vt = vtab + (long long)v * kVtab;
-            if (lane == 0) {
+                for (int b = 0; b <= a; ++b) sm.sl[warp][a * (a + 1) / 2 + b] = (a == b) ? id[a] : Lc[a * 6 + b];
+        }
+        // forward substitution, lane c <= L solves L z = column c of [B^T | g_v]
+        if (lane < NZ) {
+            double z[6];
 #pragma unroll
-                for (int a = 0; a < 6; ++a)
+            for (int i = 0; i < 6; ++i) {
+                double s = sm.sv[warp][(lane < L) ? (S::B + lane * 6 + i) : (S::GV + i)];
 #pragma unroll
-                    for (int b = 0; b <= a; ++b) sl[warp][a * (a + 1) / 2 + b] = (a == b) ? id[a] : Lc[a * 6 + b];
-            }
-            // forward substitution, lane c <= L solves L z = column c of [B^T | g_v]
-            if (lane < NZ) {
-                double z[6];
-#pragma unroll
-                for (int i = 0; i < 6; ++i) {
-                    double s = sv[warp][(lane < L) ? (S::B + lane * 6 + i) : (S::GV + i)];
-#pragma unroll
-                    for (int k = 0; k < i; ++k) s = fma(-Lc[i * 6 + k], z[k], s);
-                    z[i] = s * id[i];
-                    sz[warp][lane * 6 + i] = z[i];
-                }
-            }
-            __syncwarp();
-            if (lane < 21) vt[lane] = sl[warp][lane];     // strictly-lower factor, 1/diagonal on the diagonal
-            for (int i = lane; i < NZ * 6; i += 32) vt[21 + i] = sz[warp][i];
-            // W = Z^T Z (upper triangle) and w = Z^T z_g
-#pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                if (ep[k] >= 0) {
-                    const double* zp = &sz[warp][ep[k] * 6];
-                    const double* zc = &sz[warp][ec[k] * 6];
-                    double s = 0.0;
-#pragma unroll
-                    for (int i = 0; i < 6; ++i) s = fma(zp[i], zc[i], s);
-                    wacc[k] += s;
-                }
+                for (int k = 0; k < i; ++k) s = fma(-Lc[i * 6 + k], z[k], s);
+                z[i] = s * id[i];
+                sm.sz[warp][lane * 6 + i] = z[i];
             }
         }
         __syncwarp();
-        STAMP(d, 1, 2);
-        sv[warp][lane] = wacc[0]; sv[warp][lane + 32] = wacc[1]; sv[warp][lane + 64] = wacc[2];
-        __syncthreads();
-        if (tid < kNBD) {
-            double s = sv[0][tid];
+        if (lane < 21) vt[lane] = sm.sl[warp][lane];     // strictly-lower factor, 1/diagonal on the diagonal
+        for (int i = lane; i < NZ * 6; i += 32) vt[21 + i] = sm.sz[warp][i];
+        // W = Z^T Z (upper triangle) and w = Z^T z_g
 #pragma unroll
-            for (int k = 1; k < kBlockWarps; ++k) s += sv[k][tid];
-            d.partW[((long long)cand * nvb + grp) * kNBD + tid] = s;
+        for (int k = 0; k < 3; ++k) {
+            if (ep[k] >= 0) {
+                const double* zp = &sm.sz[warp][ep[k] * 6];
+                const double* zc = &sm.sz[warp][ec[k] * 6];
+                double s = 0.0;
+#pragma unroll
+                for (int i = 0; i < 6; ++i) s = fma(zp[i], zc[i], s);
+                wacc[k] += s;
+            }
         }
     }
-    // The last block to finish gathers, in one round trip and in a fixed order, the block rows of W,
-    // the block rows of the intrinsic sweep (A, g_c) and the block costs; it publishes the reduced
-    // system (summed over the ranks when the views are sharded) and solves it from shared memory,
-    // one warp per candidate.
-    __threadfence();
+    __syncwarp();
+    STAMP(d, 1, 2);
+    sm.sv[warp][lane] = wacc[0]; sm.sv[warp][lane + 32] = wacc[1]; sm.sv[warp][lane + 64] = wacc[2];
     __syncthreads();
-    if (tid == 0) {
-        const unsigned int prev = atomicAdd(&st->cnt_schur, 1u);
-        s_last = (prev == gridDim.x - 1);
+    if (tid < kNBD) {
+        double s = sm.sv[0][tid];
+#pragma unroll
+        for (int k = 1; k < kBlockWarps; ++k) s += sm.sv[k][tid];
+        d.partW[((long long)cand * nvb + grp) * kNBD + tid] = s;
     }
-    __syncthreads();
-    STAMP(d, 1, 3);
-    if (!s_last) return;
-    __threadfence();
+}
+
+// By ONE block once every row of partW (and, after an evaluation, of partA / partE) is visible:
+// gathers them in a fixed order (all loads of a warp in flight at once), publishes the reduced system
+// (summed over the ranks when the views are sharded) and, with fuse_solve, solves it from shared
+// memory, one warp per candidate.  Returns false when a peer never arrived at the exchange.
+template <int MODEL>
+__device__ __forceinline__ bool schur_tail(const Dev& d, SchurSmem<MODEL>& sm, const PassCtx& c, int fuse_solve) {
+    const int tid = tid_now(), lane = tid & 31, warp = tid >> 5;
+    const int nvb = d.sc_groups, J = c.J;
     // The intrinsic block, g_c and the cost at the current point: after an evaluation the block rows
-    // k_eval wrote are summed here (fixed order, all loads of a warp in flight at once) and kept in
-    // redA; while steps from this point are rejected they do not change and 65 numbers are read back.
-    if (st->need_eval) {
+    // the evaluation pass wrote are summed here and kept in redA; while steps from this point are
+    // rejected they do not change and 65 numbers are read back.
+    if (c.need_eval) {
         constexpr int R = 19;                       // rows per warp held in flight (148 blocks / 8 warps)
         double a0 = 0.0, a1 = 0.0, e = 0.0;
         for (int r0 = warp; r0 < d.ev_blocks; r0 += kBlockWarps * R) {
@@ -282,29 +272,28 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
         }
         for (int r = tid; r < d.ev_blocks; r += kBlockThreads) e = __dadd_rn(e, __ldcg(d.partE + r));
         e = warp_sum(e);
-        sga[warp][lane] = a0; sga[warp][lane + 32] = a1;
-        if (lane == 0) sge[warp] = e;
+        sm.sga[warp][lane] = a0; sm.sga[warp][lane + 32] = a1;
+        if (lane == 0) sm.sge[warp] = e;
         __syncthreads();
         if (tid < kNA) {
-            double s = sga[0][tid];
+            double s = sm.sga[0][tid];
 #pragma unroll
-            for (int k = 1; k < kBlockWarps; ++k) s += sga[k][tid];
-            sred[kRedA + tid] = s;
+            for (int k = 1; k < kBlockWarps; ++k) s += sm.sga[k][tid];
+            sm.sred[kRedA + tid] = s;
             d.redA[kRedA + tid] = s;
         } else if (tid == kNA) {
-            double s = sge[0];
+            double s = sm.sge[0];
 #pragma unroll
-            for (int k = 1; k < kBlockWarps; ++k) s = __dadd_rn(s, sge[k]);
-            sred[kRedE] = s;
+            for (int k = 1; k < kBlockWarps; ++k) s = __dadd_rn(s, sm.sge[k]);
+            sm.sred[kRedE] = s;
             d.redA[kRedE] = s;
-            st->n_eval += 1;
+            d.st->n_eval += 1;
         } else if (tid < kRedW0) {
-            sred[tid] = 0.0;
+            sm.sred[tid] = 0.0;
         }
     } else if (tid < kRedW0) {
-        sred[tid] = tid <= kRedE ? __ldcg(d.redA + tid) : 0.0;
+        sm.sred[tid] = tid <= kRedE ? __ldcg(d.redA + tid) : 0.0;
     }
-    if (tid == 0) st->cnt_schur = 0;
     STAMP(d, 1, 4);
     for (int j = 0; j < J; ++j) {
         constexpr int R = 8;                        // rows per warp held in flight
@@ -324,25 +313,57 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
             for (int k = 0; k < R; ++k) { s0 += t0[k]; s1 += t1[k]; s2 += t2[k]; }
         }
         __syncthreads();          // sv of the previous candidate has been consumed
-        sv[warp][lane] = s0; sv[warp][lane + 32] = s1; sv[warp][lane + 64] = s2;
+        sm.sv[warp][lane] = s0; sm.sv[warp][lane + 32] = s1; sm.sv[warp][lane + 64] = s2;
         __syncthreads();
         if (tid < kNBD) {
-            double s = sv[0][tid];
+            double s = sm.sv[0][tid];
 #pragma unroll
-            for (int k = 1; k < kBlockWarps; ++k) s += sv[k][tid];
-            sred[red_w(j) + tid] = s;
+            for (int k = 1; k < kBlockWarps; ++k) s += sm.sv[k][tid];
+            sm.sred[red_w(j) + tid] = s;
         }
     }
     __syncthreads();
     // views sharded over the GPUs of the node: sum the reduced systems of all ranks, right here
-    if (d.peer.nranks > 1 && !peer_allreduce(d.peer, 0, sred, red_n(J), &s_last)) {
+    if (d.peer.nranks > 1 && !peer_allreduce(d.peer, 0, sm.sred, red_n(J), &sm.s_last)) return false;
+    for (int e = tid; e < red_n(J); e += kBlockThreads) d.red[e] = sm.sred[e];
+    STAMP(d, 1, 5);
+    if (fuse_solve) solve_candidates<MODEL>(d, sm.sred, sm.sdense, c, LdPlain());
+    STAMP(d, 1, 6);
+    return true;
+}
+
+// Grid = sc_groups x kJMax blocks: block (g, j) works for candidate j of the damping ladder (and
+// leaves the view stage at once when the pass has fewer candidates); the last block to finish (atomic
+// ticket) runs the tail.
+template <int MODEL>
+__global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) {
+    pdl_trigger();
+    pdl_wait();
+    LmState* st = d.st;
+    if (st->done) return;
+    __shared__ SchurSmem<MODEL> sm;
+    const int tid = threadIdx.x;
+    const int nvb = d.sc_groups;
+    const PassCtx c = pass_ctx(*st);
+    const int cand = blockIdx.x / nvb, grp = blockIdx.x - cand * nvb;
+    STAMP(d, 1, 0);
+    if (cand < c.J) schur_views_block<MODEL>(d, sm, cand, grp, c.lam);
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        const unsigned int prev = atomicAdd(&st->cnt_schur, 1u);
+        sm.s_last = (prev == gridDim.x - 1);
+    }
+    __syncthreads();
+    STAMP(d, 1, 3);
+    if (!sm.s_last) return;
+    __threadfence();
+    if (tid == 0) st->cnt_schur = 0;
+    if (!schur_tail<MODEL>(d, sm, c, fuse_solve)) {
         if (tid == 0) { st->comm_fail = 1; st->done = 1; }
         return;
     }
-    for (int e = tid; e < red_n(J); e += kBlockThreads) d.red[e] = sred[e];
-    STAMP(d, 1, 5);
-    if (fuse_solve) solve_candidates<MODEL>(d, sred, sdense, J, LdPlain());
-    STAMP(d, 1, 6);
+    if (fuse_solve && tid == 0 && c.iter == 0) st->E_cur = sm.sred[kRedE];
 }
 
 // reduced solve as its own launch (after the all-reduce when NCCL sums the reduced systems):
@@ -353,57 +374,50 @@ __global__ void k_solve(Dev d) {
     pdl_wait();
     if (d.st->done) return;
     __shared__ double sdense[kJMax * (L * L + L)];
-    solve_candidates<MODEL>(d, d.red, sdense, d.st->J, LdCg());
+    const PassCtx c = pass_ctx(*d.st);
+    solve_candidates<MODEL>(d, d.red, sdense, c, LdCg());
+    if (threadIdx.x == 0 && c.iter == 0) d.st->E_cur = __ldcg(d.red + kRedE);
 }
 
-// ---- back-substitution, trial parameters and trial view constants: one warp per view; grid =
-// bs_groups x kJMax, block (g, j) works for candidate j ---
+// ---- back-substitution, trial parameters and trial view constants: one warp per view; block (g, j)
+// works for candidate j on views 8 g + warp + k * 8 bs_groups -----------------------------------------
+struct __align__(16) BacksubSmem {
+    ViewC sview[kBlockWarps];
+    double srow[kBlockWarps][kVtab];
+    double sx[kBlockWarps][8];
+    double sdc[kJMax][16];
+};
+
+// All threads of a block; sm.sdc must hold the shared-parameter steps of the pass (backsub_load_dc).
 template <int MODEL>
-__global__ void __launch_bounds__(kBlockThreads) k_backsub(Dev d) {
-    using T = ModelTraits<MODEL>;
-    constexpr int L = T::L;
-    pdl_trigger();
-    pdl_wait();
-    LmState* st = d.st;
-    if (st->done) return;
-    __shared__ double srow[kBlockWarps][kVtab];
-    __shared__ double sx[kBlockWarps][8];
-    __shared__ double sdc[kJMax][16];
-    __shared__ __align__(16) ViewC sview[kBlockWarps];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int cur = st->cur, J = st->J;
+__device__ __forceinline__ void backsub_block(const Dev& d, BacksubSmem& sm, int j, int grp, int cur) {
+    constexpr int L = ModelTraits<MODEL>::L;
+    const int tid = tid_now(), lane = tid & 31, warp = tid >> 5;
     const double* P = d.Pbuf + (long long)cur * d.K;
-    if (tid < kJMax * 16) {
-        const int j = tid >> 4, i = tid & 15;
-        if (j < J && i < L) sdc[j][i] = d.dcs[j * 16 + i];
-    }
-    __syncthreads();
     const int nb = d.bs_groups;
-    const int j = blockIdx.x / nb, grp = blockIdx.x - j * nb;
-    if (j >= J) return;
     const int tb = trial_buf(cur, j);
     STAMP(d, 2, 0);
     for (int v = grp * kBlockWarps + warp; v < d.M; v += nb * kBlockWarps) {
         double* Pt = d.Pbuf + (long long)tb * d.K;
         const double* vt = d.vtab + ((long long)j * d.M + v) * kVtab;
         __syncwarp();
-        srow[warp][lane] = vt[lane];
-        srow[warp][lane + 32] = vt[lane + 32];
-        if (lane + 64 < kVtab) srow[warp][lane + 64] = vt[lane + 64];
+        sm.srow[warp][lane] = vt[lane];
+        sm.srow[warp][lane + 32] = vt[lane + 32];
+        if (lane + 64 < kVtab) sm.srow[warp][lane + 64] = vt[lane + 64];
         __syncwarp();
-        const double* Lc = &srow[warp][0];          // packed lower factor
-        const double* Zm = &srow[warp][21];         // Z columns, 6 each
+        const double* Lc = &sm.srow[warp][0];          // packed lower factor
+        const double* Zm = &sm.srow[warp][21];         // Z columns, 6 each
         if (lane < 6) {
             double s = Zm[L * 6 + lane];
 #pragma unroll
-            for (int p = 0; p < L; ++p) s = fma(-Zm[p * 6 + lane], sdc[j][p], s);
-            sx[warp][lane] = s;
+            for (int p = 0; p < L; ++p) s = fma(-Zm[p * 6 + lane], sm.sdc[j][p], s);
+            sm.sx[warp][lane] = s;
         }
         __syncwarp();
         if (lane == 0) {
             double x[6];
 #pragma unroll
-            for (int i = 0; i < 6; ++i) x[i] = sx[warp][i];
+            for (int i = 0; i < 6; ++i) x[i] = sm.sx[warp][i];
 #pragma unroll
             for (int i = 5; i >= 0; --i) {
                 double s = x[i];
@@ -419,14 +433,40 @@ __global__ void __launch_bounds__(kBlockThreads) k_backsub(Dev d) {
                 Pt[idx] = e[i];
                 if (j == 0) d.delta[idx] = x[i];
             }
-            make_view(e, sview[warp]);
+            make_view(e, sm.sview[warp]);
         }
         __syncwarp();
         if (lane < kViewDoubles)
             reinterpret_cast<double*>(d.views + (long long)tb * d.M + v)[lane] =
-                reinterpret_cast<const double*>(&sview[warp])[lane];
+                reinterpret_cast<const double*>(&sm.sview[warp])[lane];
     }
     STAMP(d, 2, 1);
+}
+
+template <int MODEL>
+__device__ __forceinline__ void backsub_load_dc(const Dev& d, BacksubSmem& sm, int J) {
+    constexpr int L = ModelTraits<MODEL>::L;
+    const int tid = tid_now();
+    if (tid < kJMax * 16) {
+        const int j = tid >> 4, i = tid & 15;
+        if (j < J && i < L) sm.sdc[j][i] = d.dcs[j * 16 + i];
+    }
+    __syncthreads();
+}
+
+template <int MODEL>
+__global__ void __launch_bounds__(kBlockThreads) k_backsub(Dev d) {
+    pdl_trigger();
+    pdl_wait();
+    LmState* st = d.st;
+    if (st->done) return;
+    __shared__ BacksubSmem sm;
+    const int cur = st->cur, J = st->J;
+    backsub_load_dc<MODEL>(d, sm, J);
+    const int nb = d.bs_groups;
+    const int j = blockIdx.x / nb, grp = blockIdx.x - j * nb;
+    if (j >= J) return;
+    backsub_block<MODEL>(d, sm, j, grp, cur);
 }
 
 // ---- parity / debug kernels (not on the timed path) ------------------------------------------

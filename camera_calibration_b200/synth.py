@@ -118,11 +118,32 @@ def perturbed_initial(A, k, poses, rs, rel_A=0.01, euler_deg=0.5, trans=0.005, z
 
 
 # ---- the named configurations (BASELINE.json "configs") -------------------------------------
-def config(name, scale=1.0):
+def _dataset_range(args):
+    corners, A, k, model, W, H, lo, hi, sigma = args
+    return make_dataset(corners, A, k, model, W, H, hi - lo, sigma, view_seed_base=lo)
+
+
+def make_dataset_parallel(corners, A, k, model, width, height, numViews, noise_sigma, procs):
+    """make_dataset with the views generated by `procs` worker processes: every view is seeded by its own
+    index (src/dataset.py:64), so the result does not depend on how the views are split."""
+    if procs <= 1 or numViews < 4 * procs:
+        return make_dataset(corners, A, k, model, width, height, numViews, noise_sigma)
+    import multiprocessing as mp
+    cuts = [numViews * i // (4 * procs) for i in range(4 * procs + 1)]
+    jobs = [(corners, A, k, model, width, height, cuts[i], cuts[i + 1], noise_sigma) for i in range(4 * procs)]
+    with mp.get_context("fork").Pool(procs) as pool:
+        parts = pool.map(_dataset_range, jobs)
+    dets = [d for p in parts for d in p[0]]
+    poses = [w for p in parts for w in p[1]]
+    return dets, poses
+
+
+def config(name, scale=1.0, procs=1):
     """Returns dict(model, dets, poses, A, k, init=(A0,W0,k0) or None, width, height).
     cfg1/cfg1n/cfg2/itest use the reference's linear stage for the initial guess (stored in
     tests/golden); cfg3/cfg4/cfg5 use perturbed ground truth.  `scale` shrinks the number of
-    views of the large configurations for tests."""
+    views of the large configurations for tests; procs > 1 generates the views of the large
+    configurations in worker processes (same result)."""
     W, H = 1440, 1080
     if name in ("cfg1", "cfg1n"):
         c = checkerboard_corners(9, 6, 0.050)
@@ -140,13 +161,13 @@ def config(name, scale=1.0):
     if name == "cfg3":
         views = max(2, int(round(1000 * scale)))
         c = checkerboard_corners(40, 40, 0.30 / 39)   # ~98 % of the corners in view, ragged
-        dets, poses = make_dataset(c, A_REALISTIC, K_REALISTIC, "radtan", W, H, views, 0.1)
+        dets, poses = make_dataset_parallel(c, A_REALISTIC, K_REALISTIC, "radtan", W, H, views, 0.1, procs)
         init = perturbed_initial(A_REALISTIC, K_REALISTIC, poses, np.random.RandomState(12345))
         return dict(model=0, dets=dets, poses=poses, A=A_REALISTIC, k=K_REALISTIC, init=init)
     if name == "cfg5":
         views = max(2, int(round(10000 * scale)))
         c = checkerboard_corners(64, 64, 0.40 / 63)
-        dets, poses = make_dataset(c, A_SYNTHETIC, K_FISHEYE, "fisheye", W, H, views, 0.1)
+        dets, poses = make_dataset_parallel(c, A_SYNTHETIC, K_FISHEYE, "fisheye", W, H, views, 0.1, procs)
         init = perturbed_initial(A_SYNTHETIC, K_FISHEYE, poses, np.random.RandomState(12345))
         return dict(model=1, dets=dets, poses=poses, A=A_SYNTHETIC, k=K_FISHEYE, init=init)
     raise ValueError("unknown config " + name)

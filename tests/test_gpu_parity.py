@@ -256,21 +256,44 @@ def test_mid_size_vs_oracle():
 
 
 def test_loop_modes_identical(golden):
-    """The device-driven loop (one graph with a WHILE node) and the host-driven loop run the same
-    kernels in the same order: bit-identical traces and parameters."""
-    for case in ("itest", "cfg2"):
+    """The host-driven loop (1), the device-driven loop (2: one graph with a WHILE node) and the
+    persistent kernel (3: one cooperative launch, phases separated by grid barriers; the default) run
+    the same device code on the same partitions in the same order: bit-identical traces and parameters."""
+    for case in ("cfg1", "itest", "cfg2"):
         g = golden(case)
         prob = _problem(g)
         prob.set_loop_mode(1)
         s1, P1, i1, t1 = prob.lm_run(g["P0"], 100)
-        prob.set_loop_mode(2)
-        s2, P2, i2, t2 = prob.lm_run(g["P0"], 100)
-        assert i1 == i2 and s1 == s2
-        assert np.array_equal(t1, t2) and np.array_equal(P1, P2)
-        # and a run that is cut by maxIters stops at exactly that many iterations
-        s3, P3, i3, t3 = prob.lm_run(g["P0"], 7)
-        assert i3 == 7 and np.array_equal(t3, t1[:7])
+        for mode in (2, 3, 0):
+            prob.set_loop_mode(mode)
+            s2, P2, i2, t2 = prob.lm_run(g["P0"], 100)
+            assert i1 == i2 and s1 == s2, (case, mode, i1, i2)
+            assert np.array_equal(t1, t2) and np.array_equal(P1, P2), (case, mode)
+            if mode in (3, 0):
+                assert prob.last_run_stats()[1] == 1      # the whole refinement is one launch
+            # and a run that is cut by maxIters stops at exactly that many iterations
+            s3, P3, i3, t3 = prob.lm_run(g["P0"], 7)
+            assert i3 == 7 and np.array_equal(t3, t1[:7]), (case, mode)
         prob.close()
+
+
+def test_persistent_kernel_partitions():
+    """The persistent kernel loops over virtual blocks: more evaluation / cost blocks than SMs (small
+    segments), several view groups per block, and the bulk-copy cost sweep must all give the traces of
+    the per-launch pipeline, bit for bit."""
+    c = synth.config("cfg3", 0.05)
+    P0 = cc.Calibrator(0)._composeParameterVector(*c["init"]).ravel()
+    offs, mp, sp = cc.flatten_detections(c["dets"])
+    prob = cc.Problem(0, offs, mp, sp)
+    for seg, staging in ((0, 0), (64, 0), (0, 1), (96, 1)):
+        prob.set_segment(seg)
+        prob.set_cost_staging(staging)
+        prob.set_loop_mode(1)
+        s1, P1, i1, t1 = prob.lm_run(P0, 100)
+        prob.set_loop_mode(3)
+        s3, P3, i3, t3 = prob.lm_run(P0, 100)
+        assert i1 == i3 and s1 == s3 and np.array_equal(t1, t3) and np.array_equal(P1, P3), (seg, staging)
+    prob.close()
 
 
 def test_damping_ladder_is_invisible(golden):
@@ -281,16 +304,16 @@ def test_damping_ladder_is_invisible(golden):
         g = golden(case)
         prob = _problem(g)
         prob.set_ladder(1)
+        prob.set_loop_mode(2)
         s1, P1, i1, t1 = prob.lm_run(g["P0"], 100)
         n1 = prob.last_run_stats()[1]
         for cap in (2, 4):
-            for mode in (1, 2):
+            for mode in (1, 3, 2):
                 prob.set_ladder(cap)
                 prob.set_loop_mode(mode)
                 s2, P2, i2, t2 = prob.lm_run(g["P0"], 100)
                 assert i1 == i2 and s1 == s2, (case, cap, mode, i1, i2)
                 assert np.array_equal(t1, t2) and np.array_equal(P1, P2), (case, cap, mode)
-            prob.set_loop_mode(2)
             assert prob.last_run_stats()[1] <= n1
         rejected = np.where(t1[:, 3] == 0)[0]
         cuts = {3, i1 - 1} | ({int(rejected[0]) + 2, int(rejected[0]) + 3} if len(rejected) else set())

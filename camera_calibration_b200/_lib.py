@@ -34,7 +34,7 @@ def _nccl_include():
 
 
 def sources():
-    return [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".cu", ".cuh"))] + [HEADER]
+    return [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".cu", ".cuh", ".inc"))] + [HEADER]
 
 
 def build(force=False, verbose=False):
@@ -105,6 +105,10 @@ def lib():
                                           ctypes.POINTER(c_int)]),
         "calib_download_params": (c_int, [_vp, _d]),
         "calib_download_trace": (c_int, [_vp, c_int, _d]),
+        "calib_set_param_trace": (c_int, [_vp, c_int]),
+        "calib_download_param_trace": (c_int, [_vp, c_int, _d]),
+        "calib_multi_set_param_trace": (c_int, [_vp, c_int]),
+        "calib_multi_download_param_trace": (c_int, [_vp, c_int, _d]),
         "calib_last_run_stats": (c_int, [_vp, _d, _i64, _i64]),
         "calib_set_profiling": (c_int, [_vp, c_int]),
         "calib_kernel_time": (c_int, [_vp, c_int, _d, _i64]),
@@ -124,6 +128,17 @@ def lib():
         "calib_peer_attach": (c_int, [_vp, c_int, c_int, _vp]),
         "calib_set_transport": (c_int, [_vp, c_int]),
         "calib_transport": (c_int, [_vp]),
+        "calib_multi_create": (c_int, [ctypes.POINTER(_vp), c_int, c_i64, _i64, _d, _d, c_int, ctypes.POINTER(c_int)]),
+        "calib_multi_create_from_views": (c_int, [ctypes.POINTER(_vp), c_int, c_i64, _i64, _vp, _vp, c_int,
+                                                  ctypes.POINTER(c_int)]),
+        "calib_multi_destroy": (None, [_vp]),
+        "calib_multi_last_error": (ctypes.c_char_p, [_vp]),
+        "calib_multi_num_gpus": (c_int, [_vp]),
+        "calib_multi_num_params": (c_i64, [_vp]),
+        "calib_multi_view_bounds": (c_int, [_vp, _i64]),
+        "calib_multi_set_loop_mode": (c_int, [_vp, c_int]),
+        "calib_multi_set_ladder": (c_int, [_vp, c_int]),
+        "calib_multi_lm_run": (c_int, [_vp, _d, c_int, c_dbl, c_dbl, c_dbl, c_dbl, _d, ctypes.POINTER(c_int), _d, _d]),
         "calib_batch_create": (c_int, [ctypes.POINTER(_vp), c_int, c_i64, _i64, _i64, _d, _d, c_int]),
         "calib_batch_destroy": (None, [_vp]),
         "calib_batch_last_error": (ctypes.c_char_p, [_vp]),

@@ -302,6 +302,16 @@ class Problem:
         self._check(self._L.calib_download_trace(self._h, int(iters), dptr(t)))
         return t
 
+    def set_param_trace(self, on):
+        """record A and k of the iterate beside every trace row (what the reference prints per iteration)"""
+        self._check(self._L.calib_set_param_trace(self._h, 1 if on else 0))
+
+    def param_trace(self, iters):
+        """(iters, L): shared parameters of the iterate each iteration started from (after set_param_trace)"""
+        out = np.empty((int(iters), self.L))
+        self._check(self._L.calib_download_param_trace(self._h, int(iters), dptr(out)))
+        return out
+
     def last_run_stats(self):
         ms = ctypes.c_double()
         nl = ctypes.c_int64()
@@ -377,6 +387,119 @@ class Problem:
 
     def transport(self):
         return int(self._L.calib_transport(self._h))
+
+
+class MultiProblem:
+    """One calibration problem whose views are sharded over several GPUs of THIS process (a calib_multi_t
+    handle): the library cuts the views into contiguous ranges balanced by point count, uploads every range
+    to its device and sums the reduced system over the devices inside the kernels (NVLink peer memory).
+    Takes and returns the full-length parameter vector, like Problem."""
+
+    def __init__(self, model, view_offsets, model_pts, sensor_pts, devices):
+        self._init_common(model, np.ascontiguousarray(view_offsets, dtype=np.int64))
+        mp = as_f64(model_pts).reshape(-1, 3)
+        sp = as_f64(sensor_pts).reshape(-1, 2)
+        if len(mp) != self.N or len(sp) != self.N:
+            raise ValueError("view_offsets[-1] must equal the number of points")
+        dev = (ctypes.c_int * len(devices))(*[int(x) for x in devices])
+        rc = self._L.calib_multi_create(ctypes.byref(self._h), self.model, self.M,
+                                        self.view_offsets.ctypes.data_as(ctypes.POINTER(ctypes.c_int64)),
+                                        dptr(mp), dptr(sp), len(devices), dev)
+        self._created(rc)
+
+    def _init_common(self, model, view_offsets):
+        self.model = distortion.model_id_of(model)
+        self.L = 10 if self.model == distortion.RADTAN else 9
+        self.view_offsets = view_offsets
+        self.M = len(view_offsets) - 1
+        self.N = int(view_offsets[-1])
+        self.K = self.L + 6 * self.M
+        self._L = _lib.lib()
+        self._h = ctypes.c_void_p()
+        self.last_device_ms = 0.0
+
+    def _created(self, rc):
+        if rc != 0:
+            msg = self._L.calib_multi_last_error(None)
+            self._h = None
+            raise CalibError(rc, msg.decode() if msg else "calib_multi_create failed")
+        self.n_gpus = int(self._L.calib_multi_num_gpus(self._h))
+
+    @classmethod
+    def from_detections(cls, model, allDetections, devices, pinned=None):
+        """From the reference's own container; see Problem.from_detections."""
+        vp = _view_pointers(allDetections)
+        if vp is None:
+            out = None
+            if pinned is not None:
+                out = pinned.reserve(sum(len(m) for s, m in allDetections))
+            offs, mp, sp = flatten_detections(allDetections, out=out)
+            return cls(model, offs, mp, sp, devices)
+        counts, pm, ps = vp
+        self = cls.__new__(cls)
+        offs = np.zeros(len(counts) + 1, dtype=np.int64)
+        np.cumsum(counts, out=offs[1:])
+        self._init_common(model, offs)
+        dev = (ctypes.c_int * len(devices))(*[int(x) for x in devices])
+        rc = self._L.calib_multi_create_from_views(ctypes.byref(self._h), self.model, self.M,
+                                                   counts.ctypes.data_as(ctypes.POINTER(ctypes.c_int64)),
+                                                   pm.ctypes.data, ps.ctypes.data, len(devices), dev)
+        self._created(rc)
+        return self
+
+    def _check(self, rc):
+        if rc != 0:
+            msg = self._L.calib_multi_last_error(self._h)
+            raise CalibError(rc, msg.decode() if msg else "")
+
+    def view_bounds(self):
+        b = np.zeros(self.n_gpus + 1, dtype=np.int64)
+        self._check(self._L.calib_multi_view_bounds(self._h, b.ctypes.data_as(ctypes.POINTER(ctypes.c_int64))))
+        return b
+
+    def set_loop_mode(self, mode):
+        self._check(self._L.calib_multi_set_loop_mode(self._h, int(mode)))
+
+    def set_ladder(self, max_candidates):
+        self._check(self._L.calib_multi_set_ladder(self._h, int(max_candidates)))
+
+    def lm_run(self, P0, maxIters, lam0=1e-3, lam_min=1e-10, lam_max=1e10, err_min=1e-12, want_trace=True):
+        """Returns (sse, P, iters, trace[iters,4])."""
+        P = as_f64(P0).ravel().copy()
+        if P.size != self.K:
+            raise ValueError(f"Expected a parameter vector of {self.K} values, got {P.size}")
+        sse = ctypes.c_double()
+        iters = ctypes.c_int()
+        ms = ctypes.c_double()
+        trace = np.zeros((max(int(maxIters), 1), 4)) if want_trace else None
+        self._check(self._L.calib_multi_lm_run(
+            self._h, dptr(P), int(maxIters), lam0, lam_min, lam_max, err_min,
+            ctypes.cast(ctypes.byref(sse), _lib._d), ctypes.byref(iters),
+            dptr(trace) if want_trace else None, ctypes.cast(ctypes.byref(ms), _lib._d)))
+        self.last_device_ms = ms.value
+        return sse.value, P, iters.value, (trace[:iters.value].copy() if want_trace else None)
+
+    def set_param_trace(self, on):
+        self._check(self._L.calib_multi_set_param_trace(self._h, 1 if on else 0))
+
+    def param_trace(self, iters):
+        out = np.empty((int(iters), self.L))
+        self._check(self._L.calib_multi_download_param_trace(self._h, int(iters), dptr(out)))
+        return out
+
+    def last_run_stats(self):
+        return self.last_device_ms, self.n_gpus, 0
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.calib_multi_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 class BatchProblem:
@@ -503,15 +626,64 @@ class Calibrator:
     _λmax = 1e+10
     _Pt_error_min = 1e-12
 
-    def __init__(self, distortionModel, device=0):
+    def __init__(self, distortionModel, device=0, devices=None, keepResident=False):
+        """devices=[0, 1, ...]: refineCalibrationParameters shards the views over these GPUs of this process
+        (MultiProblem); everything else runs on devices[0].
+        keepResident=True: the detections of the last refineCalibrationParameters call stay on the device(s);
+        a following call that passes THE SAME list object (same length, same first / last arrays) runs on
+        them without gathering and uploading again -- the reference's re-entry pattern, src/animate.py:40-42
+        (maxIters=1, 50 times over one allDetections).  Opt-in because it trusts the caller not to rewrite
+        the arrays in place between calls; release() drops the device copy."""
         self._distortionModel = distortionModel
         self._model = distortion.model_id_of(distortionModel)
-        self._device = device
+        self._devices = [int(x) for x in devices] if devices is not None and len(devices) > 1 else None
+        self._device = int(devices[0]) if devices is not None and len(devices) >= 1 else device
         self._jac = None
         self.lastTrace = None     # (iters,4): E, E', lambda, accepted
         self.lastIters = 0
         self.lastDeviceMs = 0.0
         self._pinned = PinnedBuffers()
+        self._keep = bool(keepResident)
+        self._resident = None      # (key, problem)
+        self.uploadCount = 0       # detections sent to the device(s) by refineCalibrationParameters so far
+
+    def release(self):
+        """drops the device copy kept by keepResident"""
+        if self._resident is not None:
+            self._resident[1].close()
+            self._resident = None
+
+    def __del__(self):
+        try:
+            self.release()
+        except Exception:
+            pass
+
+    @staticmethod
+    def _detections_key(allDetections):
+        n = len(allDetections)
+        if n == 0:
+            return (id(allDetections), 0)
+        s0, m0 = allDetections[0]
+        s1, m1 = allDetections[-1]
+        return (id(allDetections), n, id(s0), id(m0), id(s1), id(m1), np.shape(s0), np.shape(s1))
+
+    def _problem_for(self, allDetections):
+        """(problem, owned): the device-side problem of these detections; owned = close it after the call"""
+        key = self._detections_key(allDetections) if self._keep else None
+        if self._keep and self._resident is not None:
+            if self._resident[0] == key:
+                return self._resident[1], False
+            self.release()
+        if self._devices is not None:
+            prob = MultiProblem.from_detections(self._model, allDetections, self._devices, pinned=self._pinned)
+        else:
+            prob = Problem.from_detections(self._model, allDetections, self._device, pinned=self._pinned)
+        self.uploadCount += 1
+        if self._keep:
+            self._resident = (key, prob)
+            return prob, False
+        return prob, True
 
     # -- entry points -----------------------------------------------------------------------
     def calibrate(self, allDetections, maxIters, initial=None):
@@ -569,27 +741,37 @@ class Calibrator:
             # the reference returns an unbound Pt_error (src/calibrate.py:171)
             raise UnboundLocalError("cannot access local variable 'Pt_error' where it is not "
                                     "associated with a value")
-        prob = Problem.from_detections(self._model, allDetections, self._device, pinned=self._pinned)
+        prob, owned = self._problem_for(allDetections)
         try:
             return self._refine_on(prob, Ainitial, Winitial, kInitial, maxIters, shouldPrint)
         finally:
-            prob.close()
+            if owned:
+                prob.close()
 
     def _refine_on(self, prob, Ainitial, Winitial, kInitial, maxIters, shouldPrint):
         if int(maxIters) <= 0:
             raise UnboundLocalError("cannot access local variable 'Pt_error' where it is not "
                                     "associated with a value")
-        ts = time.time()
         Pt = self._composeParameterVector(Ainitial, Winitial, kInitial)
+        prob.set_param_trace(bool(shouldPrint))
+        ts = time.time()
         sse, P, iters, trace = prob.lm_run(Pt, int(maxIters), self._λinitial, self._λmin,
                                            self._λmax, self._Pt_error_min)
+        elapsed = time.time() - ts
         self.lastDeviceMs = prob.last_run_stats()[0]
         self.lastTrace, self.lastIters = trace, iters
         if shouldPrint:
-            for it, (E, E1, lam, acc) in enumerate(trace):
-                print(f"\niter {it}: error={min(E1, E):0.3f}, λ={lam:e}")
-            At, Wt, kt = self._decomposeParameterVector(P)
-            print(f"({time.time() - ts:0.3f}s)\nA:\n{At}\nk:\n{kt}")
+            # src/calibrate.py:158-159, 269-274: per iteration the time since the loop started, min(E', E),
+            # lambda, then A and k of the iterate BEFORE the update.  The loop ran on the device in one go:
+            # the per-iteration times are its wall time spread evenly over the iterations.
+            nd = self._numDistortion()
+            for it, ((E, E1, lam, acc), row) in enumerate(zip(trace, prob.param_trace(iters))):
+                α, β, γ, uc, vc = row[:5]
+                At = np.array([[α, γ, uc], [0, β, vc], [0, 0, 1]])
+                print(f"\niter {it}: ({elapsed * (it + 1) / iters:0.3f}s), error={min(E1, E):0.3f}, "
+                      f"λ={lam:e}")
+                print(f"A:\n{At}")
+                print(f"k:\n{row[5:5 + nd]}")
         Arefined, Wrefined, kRefined = self._decomposeParameterVector(P)
         return sse, Arefined, Wrefined, kRefined
 
@@ -651,10 +833,11 @@ class Calibrator:
         return A, list(Wall), P[5:start]
 
 
-def calibrateCamera(allDetections, distortionType, maxIters, initial=None, device=0):
+def calibrateCamera(allDetections, distortionType, maxIters, initial=None, device=0, devices=None):
     """src/main.py:11-36 on the GPU path: closed-form initial estimate and LM refinement on one device
     handle.  `initial` = (A, W, k) skips the estimate; ValueError on an unknown distortion type as in
-    the reference.  Returns (sse, Afinal, Wfinal, kFinal)."""
+    the reference.  devices=[...]: the refinement shards the views over these GPUs (the initial estimate
+    runs on the first).  Returns (sse, Afinal, Wfinal, kFinal)."""
     model = distortion.model_id_of(distortionType)
-    calibrator = Calibrator(model, device)
+    calibrator = Calibrator(model, device, devices=devices)
     return calibrator.calibrate(allDetections, maxIters, initial=initial)

@@ -18,7 +18,10 @@
 #include <vector>
 
 #include "../../include/calib_b200.h"
-#include "calib_persistent.cuh"
+#include "calib_solve.cuh"
+#ifdef CALIB_EXPERIMENT_PERSISTENT
+#include "experiments/calib_persistent.cuh"     // loop mode 3: measured, not faster, not in the default build
+#endif
 #include "calib_batch.cuh"
 #include "calib_homography.cuh"
 #include "calib_linear.cuh"
@@ -47,10 +50,11 @@ static void free_pool(std::vector<void*>& pool, cudaStream_t stream) {
 struct PeerComm {
     int nranks = 1, rank = 0, device = 0;
     uint4* inbox = nullptr;                  // cudaMalloc: kPeerInboxBytes, then the counters
-    void* mapped[kPeerMaxRanks] = {};        // peers' inboxes (cudaIpcOpenMemHandle)
+    void* mapped[kPeerMaxRanks] = {};        // peers' inboxes (cudaIpcOpenMemHandle; plain pointers in one process)
+    bool ipc = true;                         // false: single-process handle, peers reached through peer access
     ~PeerComm() {
         cudaSetDevice(device);
-        for (void* m : mapped) if (m) cudaIpcCloseMemHandle(m);
+        if (ipc) for (void* m : mapped) if (m) cudaIpcCloseMemHandle(m);
         if (inbox) cudaFree(inbox);
     }
     bool mapped_ok() const {
@@ -97,6 +101,9 @@ struct calib_handle {
     int transport = 0;                     // 0 auto (peer memory when attached, else NCCL), 1 NCCL, 2 peer memory
     double* l2buf = nullptr;
     size_t l2bytes = 0;
+    bool want_ptrace = false;              // calib_set_param_trace
+    bool run_pending = false;              // lm_start enqueued a whole-loop launch that lm_finish has not collected yet
+    int64_t pending_count = 0;
 };
 
 #define CUDA_TRY(h, call)                                                                     \
@@ -317,7 +324,7 @@ static int build_tasks(calib_handle* h, int seg, bool sync_now = true) {
         ev_warps = co_warps = (int)std::max<int64_t>(1, (N + seg - 1) / seg);
     } else {
         const int64_t by_size = std::max<int64_t>(1, (N + 63) / 64);
-        ev_warps = (int)std::min<int64_t>((int64_t)h->n_sm * kBlockWarps, by_size);
+        ev_warps = (int)std::min<int64_t>((int64_t)h->n_sm * kEvalPairs, by_size);      // one chunk per producer / consumer pair
         co_warps = (int)std::min<int64_t>((int64_t)h->n_sm * kBlockWarps * 2, by_size);
     }
     std::vector<Piece> evp, cop;
@@ -333,7 +340,7 @@ static int build_tasks(calib_handle* h, int seg, bool sync_now = true) {
         vp[M] = (int)evp.size();
     }
     Dev& d = h->dev;
-    d.ev_warps = ev_warps; d.ev_blocks = (ev_warps + kBlockWarps - 1) / kBlockWarps; d.ev_pieces = (int)evp.size();
+    d.ev_warps = ev_warps; d.ev_blocks = (ev_warps + kEvalPairs - 1) / kEvalPairs; d.ev_pieces = (int)evp.size();
     d.co_warps = co_warps; d.co_blocks = (co_warps + kBlockWarps - 1) / kBlockWarps;
     // k_schur / k_backsub: one warp per view; the grid repeats the view groups once per candidate
     // of the damping ladder (blocks of candidates a pass does not have leave at once)
@@ -379,15 +386,17 @@ static int ensure_trace(calib_handle* h, int iters) {
     if (iters <= h->trace_cap) return CALIB_OK;
     drop_graph(h);
     double* t = nullptr;
-    CUDA_TRY(h, cudaMalloc((void**)&t, (size_t)iters * 4 * sizeof(double)));
+    CUDA_TRY(h, cudaMalloc((void**)&t, (size_t)iters * 20 * sizeof(double)));
     if (h->trace_own) cudaFree(h->trace_own);
     h->trace_own = t;
     h->dev.trace = t;
+    h->dev.ptrace = t + 4 * (size_t)iters;
     h->trace_cap = iters;
     return CALIB_OK;
 }
 
 namespace {
+int default_loop_mode(const calib_handle* h);
 bool cost_uses_tma(const calib_handle* h);
 int build_loop_graph(calib_handle* h);
 void apply_transport(calib_handle* h);
@@ -531,11 +540,17 @@ static cudaError_t device_func_attributes(int device) {
     std::lock_guard<std::mutex> lk(mu);
     if (device >= 0 && device < 64 && done[device]) return cudaSuccess;
     cudaError_t e = cudaSuccess;
-    auto set = [&](auto kern) {
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCostDynSmem);
+    auto set = [&](auto kern, size_t bytes) {
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     };
-    set(k_cost<0, false, true>); set(k_cost<0, true, true>); set(k_cost<1, false, true>); set(k_cost<1, true, true>);
-    set(k_lm_persistent<0, true, 1>); set(k_lm_persistent<1, true, 1>);
+    set(k_cost<0, false, true>, kCostDynSmem); set(k_cost<0, true, true>, kCostDynSmem);
+    set(k_cost<1, false, true>, kCostDynSmem); set(k_cost<1, true, true>, kCostDynSmem);
+    set(k_eval<0>, kEvalDynSmem); set(k_eval<1>, kEvalDynSmem);
+#ifdef CALIB_EXPERIMENT_PERSISTENT
+    set(k_lm_persistent<0, true, 1>, kPersistDynSmem); set(k_lm_persistent<1, true, 1>, kPersistDynSmem);
+    set(k_lm_persistent<0, false, 1>, kPersistDynSmem); set(k_lm_persistent<1, false, 1>, kPersistDynSmem);
+    set(k_lm_persistent<0, false, 2>, kPersistDynSmem); set(k_lm_persistent<1, false, 2>, kPersistDynSmem);
+#endif
     if (e == cudaSuccess && device >= 0 && device < 64) done[device] = true;
     return e;
 }
@@ -590,7 +605,7 @@ static int create_impl(calib_t** out, int model, int64_t M, const int64_t* view_
 #endif
         const size_t o_st = a.reserve<LmState>(1);
         constexpr int kTraceIters = 256;
-        const size_t o_trace = a.reserve<double>(4 * kTraceIters);
+        const size_t o_trace = a.reserve<double>(20 * kTraceIters);     // trace rows, then the parameter trace
         const size_t zero_from = o_P, zero_bytes = a.bytes - o_P;
         const size_t o_aos = a.reserve<double>(5 * n);     // upload staging, AoS as the caller holds it
         TRY_(cudaMallocAsync(&h->arena_fixed, a.bytes, h->stream));
@@ -605,6 +620,7 @@ static int create_impl(calib_t** out, int model, int64_t M, const int64_t* view_
 #endif
         d.st = a.at<LmState>(o_st);
         d.trace = a.at<double>(o_trace);
+        d.ptrace = d.trace + 4 * kTraceIters;
         h->trace_cap = kTraceIters;
         TRY_(cudaMemsetAsync(a.base + zero_from, 0, zero_bytes, h->stream));
         if (N > 0) {
@@ -640,8 +656,9 @@ static int create_impl(calib_t** out, int model, int64_t M, const int64_t* view_
             apply_transport(h);
         }
     }
-    // (the default loop is the persistent kernel: no graph to build; loop modes 1 and 2 build theirs on
-    // first use)
+    // the default loop graph is built here, on the host, while the detections are still crossing PCIe
+    // (a setting that changes the iteration drops it and lm_run rebuilds it)
+    if (default_loop_mode(h) == 2 && build_loop_graph(h) != CALIB_OK) { cudaGetLastError(); drop_graph(h); }
     empty_trash(device_id, 0);      // graphs of destroyed handles: torn down while the detections cross PCIe
     if (uploader.joinable() || upload_inline) {
         if (uploader.joinable()) uploader.join();
@@ -715,7 +732,11 @@ extern "C" int calib_set_segment(calib_t* h, int points_per_task) {
 
 extern "C" int calib_set_loop_mode(calib_t* h, int mode) {
     if (!h) return fail(nullptr, CALIB_E_ARG, "NULL handle");
+#ifdef CALIB_EXPERIMENT_PERSISTENT
     if (mode < 0 || mode > 3) return fail(h, CALIB_E_ARG, "calib_set_loop_mode: 0 auto, 1 host, 2 device graph, 3 persistent kernel");
+#else
+    if (mode < 0 || mode > 2) return fail(h, CALIB_E_ARG, "calib_set_loop_mode: 0 auto, 1 host, 2 device");
+#endif
     h->loop_mode = mode;
     return CALIB_OK;
 }
@@ -832,7 +853,7 @@ void enqueue_eval(calib_handle* h, Launcher& ln) {
     const Dev& d = h->dev;
     cudaEvent_t a, b;
     ln.begin(&a, &b);
-    launch_iter(h, k_eval<MODEL>, d.ev_blocks, kBlockThreads, 0, d);
+    launch_iter(h, k_eval<MODEL>, d.ev_blocks, kBlockThreads, kEvalDynSmem, d);
     ln.end(KEVAL, a, b);
     ln.count += 1;
 }
@@ -881,6 +902,19 @@ void enqueue_cost(calib_handle* h, Launcher& ln, int fuse_accept) {
     }
     ln.end(KCOST, a, b);
     ln.count += 1;
+}
+
+bool peer_active(const calib_handle* h);
+bool nccl_active(const calib_handle* h);
+// Loop mode 0 (automatic): the WHILE graph; NCCL collectives cannot sit inside a WHILE body, that transport is
+// driven by the host.  (A persistent cooperative kernel with grid barriers between the phases was built and
+// measured, profiles/r2b_*, r2c_*: a grid barrier costs what a kernel boundary inside the WHILE graph costs,
+// 1.5-2 us, and the phases run no faster, so it is not in the default build: csrc/experiments/.)
+// CALIB_LOOP_MODE overrides.
+int default_loop_mode(const calib_handle* h) {
+    static const int env = [] { const char* e = getenv("CALIB_LOOP_MODE"); return e ? atoi(e) : 0; }();
+    if (nccl_active(h)) return 1;
+    return env >= 1 && env <= 2 ? env : 2;
 }
 
 bool peer_active(const calib_handle* h) {
@@ -1002,6 +1036,7 @@ int push_state(calib_handle* h, double lam, double lam_min, double lam_max, doub
     s.lam = lam; s.lam_min = lam_min; s.lam_max = lam_max; s.err_min = err_min;
     s.max_iters = max_iters; s.need_eval = 1; s.cur = h->cur; s.nranks = h->nranks;
     s.J = 1; s.jmax = std::max(1, std::min(jmax, (int)kJMax));
+    s.want_ptrace = h->want_ptrace ? 1 : 0;
     *h->h_state = s;
     CUDA_TRY(h, cudaMemcpyAsync(h->dev.st, h->h_state, sizeof(LmState), cudaMemcpyHostToDevice, h->stream));
     return CALIB_OK;
@@ -1030,17 +1065,19 @@ int check_handle(calib_handle* h) {
 
 }  // namespace
 
-// ---- the persistent kernel (calib_persistent.cuh) ---------------------------------------------------
+// ---- the persistent kernel (experiments/calib_persistent.cuh; -DCALIB_EXPERIMENT_PERSISTENT) ---------------------------------------------------
 namespace {
 bool cost_uses_tma(const calib_handle* h) {
     // bulk-copy ring when the detections cannot stay in L2 between the sweeps, plain loads otherwise
     return h->cost_tma >= 0 ? h->cost_tma != 0 : (size_t)h->N * 40 > ((size_t)96 << 20);
 }
 
+#ifdef CALIB_EXPERIMENT_PERSISTENT
+
 template <int MODEL, bool TMA, int PF>
 int launch_persistent_t(calib_handle* h) {
     auto kern = k_lm_persistent<MODEL, TMA, PF>;
-    const size_t smem = TMA ? kCostDynSmem : 0;
+    const size_t smem = kPersistDynSmem;     // the evaluation pass's hand-off rings / the cost pass's bulk-copy rings
     if (h->persist_blocks <= 0) {
         int per_sm = 0;
         CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kBlockThreads, smem));
@@ -1067,6 +1104,9 @@ int launch_persistent(calib_handle* h) {
     if (tma) return launch_persistent_t<1, true, 1>(h);
     return pf == 2 ? launch_persistent_t<1, false, 2>(h) : launch_persistent_t<1, false, 1>(h);
 }
+#else
+int launch_persistent(calib_handle* h) { return fail(h, CALIB_E_STATE, "loop mode 3 is not in this build"); }
+#endif
 }  // namespace
 
 // ---- LM loop ------------------------------------------------------------------------------------
@@ -1094,12 +1134,15 @@ extern "C" int calib_download_trace(calib_t* h, int iters, double* trace) {
     return sync(h);
 }
 
-extern "C" int calib_lm_run_resident(calib_t* h, int maxIters, double lam0, double lam_min,
-                                     double lam_max, double err_min, double* sse_out, int* iters_out) {
-    RC(check_handle(h));
-    if (maxIters <= 0)
-        return fail(h, CALIB_E_STATE, "calib_lm_run: maxIters <= 0 (the reference raises UnboundLocalError)");
-    ScopeTimer tm_("calib_lm_run_resident");
+// The loop in two halves so that one host thread can start it on several devices before waiting for any
+// (calib_multi.inc).  lm_start: everything up to and including the launch(es) of loop modes 2 / 3 and the
+// read-back of the state; returns with the work in flight (run_pending).  Loop mode 1 and profiling runs
+// are driven by the host and complete inside lm_start.
+namespace {
+int lm_finish(calib_handle* h);
+
+int lm_start(calib_handle* h, int maxIters, double lam0, double lam_min, double lam_max, double err_min) {
+    ScopeTimer tm_("lm_start");
     RC(ensure_trace(h, maxIters));
     const bool prof = h->profiling;
     // the device-driven loop needs every node of the body on this GPU; with a communicator the
@@ -1110,10 +1153,9 @@ extern "C" int calib_lm_run_resident(calib_t* h, int maxIters, double lam0, doub
     if (h->loop_mode == 3 && nccl_active(h))
         return fail(h, CALIB_E_STATE, "loop mode 3: the persistent kernel sums over the ranks through peer memory "
                                       "(calib_peer_attach); NCCL all-reduces need loop mode 1");
-    // default: the persistent kernel (one cooperative launch per refinement) on one GPU and with the
-    // peer-memory transport; iteration graphs driven by the host with NCCL
-    const bool persistent = !prof && (h->loop_mode == 3 || (h->loop_mode == 0 && !nccl_active(h)));
-    const bool device_loop = !prof && h->loop_mode == 2;
+    const int mode = h->loop_mode ? h->loop_mode : default_loop_mode(h);
+    const bool persistent = !prof && mode == 3;
+    const bool device_loop = !prof && mode == 2;
     if (!prof && !persistent) {
         int rc = device_loop ? build_loop_graph(h) : build_graph(h);
         if (rc && h->pdl) {          // a driver that rejects programmatic edges here: plain edges
@@ -1136,18 +1178,12 @@ extern "C" int calib_lm_run_resident(calib_t* h, int maxIters, double lam0, doub
         ln.count = 1;
         CUDA_TRY(h, cudaMemcpyAsync(h->h_state, h->dev.st, sizeof(LmState), cudaMemcpyDeviceToHost, h->stream));
         CUDA_TRY(h, cudaEventRecord(h->ev1, h->stream));
-        RC(sync(h));
-        if (h->h_state->bar_abort)
-            return fail(h, CALIB_E_CUDA, "persistent kernel: a block waited too long at a grid barrier (grid not co-resident?)");
     } else if (device_loop) {
         RC(make_views(h, 1));
         ln.count = 1;
         CUDA_TRY(h, cudaGraphLaunch(h->loop_graph, h->stream));
         CUDA_TRY(h, cudaMemcpyAsync(h->h_state, h->dev.st, sizeof(LmState), cudaMemcpyDeviceToHost, h->stream));
         CUDA_TRY(h, cudaEventRecord(h->ev1, h->stream));
-        RC(sync(h));
-        // skipped evaluations (after a rejected step) still launch and return at once
-        ln.count += (int64_t)kpi * h->h_state->n_pass;
     } else {
         RC(make_views(h, 1));
         ln.count = 1;
@@ -1166,12 +1202,30 @@ extern "C" int calib_lm_run_resident(calib_t* h, int maxIters, double lam0, doub
             batch = std::min(batch * 2, 16);
         }
         CUDA_TRY(h, cudaEventRecord(h->ev1, h->stream));
-        RC(sync(h));
+    }
+    h->pending_count = ln.count;
+    h->run_pending = true;
+    return CALIB_OK;
+}
+
+int lm_finish(calib_handle* h) {
+    if (!h->run_pending) return fail(h, CALIB_E_STATE, "lm_finish: no run in flight");
+    h->run_pending = false;
+    RC(sync(h));
+    const int mode = h->loop_mode ? h->loop_mode : default_loop_mode(h);
+    int64_t count = h->pending_count;
+    if (!h->profiling && mode == 2)      // skipped evaluations (after a rejected step) still launch and return at once
+        count += (int64_t)kernels_per_iteration(h) * h->h_state->n_pass;
+    if (h->h_state->bar_abort) {
+        char b[160];
+        snprintf(b, sizeof b, "a wait inside the kernels timed out (code %d: 1 grid barrier of the persistent kernel, 2 / 3 "
+                              "producer / consumer hand-off of the evaluation pass)", h->h_state->bar_abort);
+        return fail(h, CALIB_E_CUDA, b);
     }
     float ms = 0;
     CUDA_TRY(h, cudaEventElapsedTime(&ms, h->ev0, h->ev1));
     h->last_ms = ms;
-    h->last_launches = ln.count;
+    h->last_launches = count;
     h->last_evals = h->h_state->n_eval;
     h->cur = h->h_state->cur;
     for (auto& pe : h->prof_events) {
@@ -1179,11 +1233,40 @@ extern "C" int calib_lm_run_resident(calib_t* h, int maxIters, double lam0, doub
         cudaEventElapsedTime(&t, pe.second.first, pe.second.second);
         h->ktime[pe.first] += t; h->kcount[pe.first] += 1;
     }
-    if (sse_out) *sse_out = h->h_state->sse;
-    if (iters_out) *iters_out = h->h_state->iter;
     if (h->h_state->comm_fail)
         return fail(h, CALIB_E_COMM, "a peer rank never arrived at the in-kernel all-reduce (timeout)");
     return CALIB_OK;
+}
+}  // namespace
+
+extern "C" int calib_set_param_trace(calib_t* h, int on) {
+    if (!h) return fail(nullptr, CALIB_E_ARG, "NULL handle");
+    h->want_ptrace = on != 0;
+    return CALIB_OK;
+}
+
+extern "C" int calib_download_param_trace(calib_t* h, int iters, double* out) {
+    RC(check_handle(h));
+    if (!out || iters < 0 || iters > h->trace_cap) return fail(h, CALIB_E_ARG, "calib_download_param_trace: bad args");
+    if (!h->want_ptrace) return fail(h, CALIB_E_STATE, "calib_download_param_trace: calib_set_param_trace(h, 1) before the run");
+    std::vector<double> tmp((size_t)iters * 16);
+    CUDA_TRY(h, cudaMemcpyAsync(tmp.data(), h->dev.ptrace, tmp.size() * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    RC(sync(h));
+    for (int i = 0; i < iters; ++i) memcpy(out + (size_t)i * h->L, tmp.data() + (size_t)i * 16, (size_t)h->L * sizeof(double));
+    return CALIB_OK;
+}
+
+extern "C" int calib_lm_run_resident(calib_t* h, int maxIters, double lam0, double lam_min,
+                                     double lam_max, double err_min, double* sse_out, int* iters_out) {
+    RC(check_handle(h));
+    if (maxIters <= 0)
+        return fail(h, CALIB_E_STATE, "calib_lm_run: maxIters <= 0 (the reference raises UnboundLocalError)");
+    ScopeTimer tm_("calib_lm_run_resident");
+    RC(lm_start(h, maxIters, lam0, lam_min, lam_max, err_min));
+    const int rc = lm_finish(h);
+    if (sse_out) *sse_out = h->h_state->sse;
+    if (iters_out) *iters_out = h->h_state->iter;
+    return rc;
 }
 
 extern "C" int calib_lm_run(calib_t* h, double* P_inout, int maxIters, double lam0, double lam_min,
@@ -1864,3 +1947,5 @@ extern "C" int calib_debug_stamps(calib_t* h, const double* P, double lam, unsig
     return CALIB_OK;
 }
 #endif
+
+#include "calib_multi.inc"

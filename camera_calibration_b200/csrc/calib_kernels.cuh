@@ -55,6 +55,7 @@ struct LmState {
     int n_pass;            // passes (one k_schur/k_backsub/k_cost each) so far
     unsigned int cnt_schur, cnt_cost, cnt_eval, pad1;
     long long n_eval;   // Jacobian evaluations actually executed
+    int want_ptrace;          // record the L shared parameters of the iterate beside every trace row
     unsigned int bar_count;   // persistent kernel: arrivals at its grid barriers so far (calib_persistent.cuh)
     int bar_abort;            // persistent kernel: a block gave up waiting at a barrier
 };
@@ -86,6 +87,7 @@ struct Dev {  // everything the kernels need; passed by value
     double* delta;                        // K
     double* dcs;                          // kJMax x 16: step of the shared parameters, per candidate
     double* trace;                        // max_iters x 4
+    double* ptrace;                       // max_iters x 16: shared parameters of the iterate each row started from
     LmState* st;
     cudaGraphConditionalHandle cond;      // WHILE node of the whole-loop graph
     int use_cond;
@@ -210,6 +212,48 @@ __device__ __forceinline__ void accum_BD(const PointOut<MODEL>& o, double (&acc)
         for (int b = j; b < 6; ++b)
             acc[S::dd(j, b)] = fma(o.ju[j], o.ju[b], fma(o.jv[j], o.jv[b], acc[S::dd(j, b)]));
         acc[S::GV + j] = fma(o.ju[j], o.ru, fma(o.jv[j], o.rv, acc[S::GV + j]));
+    }
+}
+
+// The same sums from a hand-off slot of the evaluation pass (calib_passes.cuh): slot[k * 32] = pair k of
+// this lane, pairs (xd,yd) (ru,rv) (ku,kv)[ND] (ju,jv)[6].  Every running sum gets the same single update per
+// point as in accum_BD (bit-identical); only the order in which the inputs are touched differs: the
+// six extrinsic column pairs are held, the left factors stream through two at a time, so that 14
+// input values are live at once instead of 26 beside the 87 sums.
+template <int MODEL>
+__device__ __forceinline__ void accum_BD_ring(const double2* slot, double (&acc)[kNBD]) {
+    constexpr int ND = ModelTraits<MODEL>::ND, L = ModelTraits<MODEL>::L;
+    using S = SlotsBD<L>;
+    double ju[6], jv[6];
+#pragma unroll
+    for (int j = 0; j < 6; ++j) { const double2 t = slot[(2 + ND + j) * 32]; ju[j] = t.x; jv[j] = t.y; }
+    {
+        const double2 r = slot[1 * 32];                  // (ru, rv)
+#pragma unroll
+        for (int j = 0; j < 6; ++j) {
+            acc[S::B + 3 * 6 + j] += ju[j];                                   // uc
+            acc[S::B + 4 * 6 + j] += jv[j];                                   // vc
+#pragma unroll
+            for (int b = j; b < 6; ++b)
+                acc[S::dd(j, b)] = fma(ju[j], ju[b], fma(jv[j], jv[b], acc[S::dd(j, b)]));
+            acc[S::GV + j] = fma(ju[j], r.x, fma(jv[j], r.y, acc[S::GV + j]));
+        }
+    }
+    {
+        const double2 x = slot[0 * 32];                  // (xd, yd)
+#pragma unroll
+        for (int j = 0; j < 6; ++j) {
+            acc[S::B + 0 * 6 + j] = fma(x.x, ju[j], acc[S::B + 0 * 6 + j]);   // alpha
+            acc[S::B + 1 * 6 + j] = fma(x.y, jv[j], acc[S::B + 1 * 6 + j]);   // beta
+            acc[S::B + 2 * 6 + j] = fma(x.y, ju[j], acc[S::B + 2 * 6 + j]);   // gamma
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < ND; ++a) {
+        const double2 k = slot[(2 + a) * 32];            // (ku_a, kv_a)
+#pragma unroll
+        for (int j = 0; j < 6; ++j)
+            acc[S::B + (5 + a) * 6 + j] = fma(k.x, ju[j], fma(k.y, jv[j], acc[S::B + (5 + a) * 6 + j]));
     }
 }
 

@@ -39,87 +39,198 @@ __device__ __forceinline__ PassCtx pass_ctx(const LmState& st) {
 }
 
 // ---- the fused evaluation pass ----------------------------------------------------------------
+// Producer / consumer warp pairs.  A point's 2 x (L+6) Jacobian rows feed 143 running sums (56 of
+// the intrinsic block A, g_c and the cost; 87 of B_v, D_v, g_v): more than one thread can hold.  The
+// first version swept the points twice with ONE warp (projection chain re-evaluated in the second
+// sweep: 416 FP64 instructions per point, 62 % of the FP64 issue rate because two warps per scheduler
+// cannot cover the ~60-deep dependent projection chain).  Here a PAIR of warps shares one sweep:
+//   producer   loads the point, runs point_eval once (the dependent chain), accumulates A, g_c, E in
+//              its registers and hands the 2 x (8 + ND) values the view blocks need to the consumer
+//              through a small ring in shared memory (one 16-byte slot per lane and value pair);
+//   consumer   accumulates B_v, D_v, g_v -- 144 independent FMAs per point, no chain, no global
+//              load -- and writes one row per piece.
+// 347 FP64 instructions per point instead of 416, and the scheduler always has the consumer's
+// independent FMAs to issue while the producer waits on its chain (pairs are warps w and w + 4: same
+// scheduler).  Per-lane accumulation order is that of the two-sweep version.
+constexpr int kEvalPairs = kBlockWarps / 2;
+constexpr int kEvalStages = 4;
+template <int MODEL> struct EvalRing {
+    static constexpr int NV2 = 8 + ModelTraits<MODEL>::ND;      // (xd,yd) (ru,rv) (ku,kv)[ND] (ju,jv)[6]
+    double2 v[kEvalStages][NV2][32];
+};
+constexpr size_t kEvalDynSmem = kEvalPairs * sizeof(EvalRing<0>);     // the radtan ring is the larger one
+
 struct __align__(16) EvalSmem {
-    ViewC sview[kBlockWarps][1];
+    ViewC sview[kEvalPairs];
     double sc[16];
-    double sred[kBlockWarps][kNA];
-    double sE[kBlockWarps];
+    double sred[kEvalPairs][kNA];
+    double sE[kEvalPairs];
+    unsigned long long full[kEvalPairs][kEvalStages], empty[kEvalPairs][kEvalStages];
 };
 
-// Block *vbp of the evaluation pass (warps vb * 8 .. vb * 8 + 7 of the partition, rec = this warp's
-// record) at the point in parameter buffer `cur`: writes the piece rows of its warps and row vb of
-// partA / partE.  vbp points to shared memory written before the call (not necessarily synchronised:
-// it is read after the first barrier below) -- the index is needed after the sweeps only and must not
-// cost a register inside them.  Called by all threads of a block; ends without a barrier after its
-// last shared-memory reads.
+// try_wait with a way out: a hand-off partner that never arrives (a bug, not a run-time condition) must
+// not hang the GPU.  After ~2 s the waiter raises the state's abort flag -- every other wait of the launch
+// then falls through at once -- and the host reports the run as failed.
+__device__ __forceinline__ bool mbar_try(unsigned long long* bar, unsigned parity) {
+    unsigned ok;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n" : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait_guarded(unsigned long long* bar, unsigned parity, LmState* st, int who) {
+    if (mbar_try(bar, parity)) return;
+    const unsigned long long t0 = global_timer_ns();
+    unsigned spins = 0;
+    while (!mbar_try(bar, parity)) {
+        if ((++spins & 63u) == 0) {
+            if (*(volatile int*)&st->bar_abort) return;
+            if (global_timer_ns() - t0 > 2000000000ull) {
+                *(volatile int*)&st->bar_abort = 2 + who; return;
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// Block *vbp of the evaluation pass (pairs vb * 4 .. vb * 4 + 3 of the partition, rec = the record of
+// this warp's pair) at the point in parameter buffer `cur`: writes the piece rows of its pairs and row
+// vb of partA / partE.  vbp points to shared memory written before the call (not necessarily
+// synchronised: it is read after the barriers below) -- the index is needed after the sweep only and
+// must not cost a register inside it.  Called by all threads of a block; ends without a barrier after
+// its last shared-memory reads.  The ring lives in dynamic shared memory (kEvalDynSmem).
 template <int MODEL>
 __device__ __forceinline__ void eval_block(const Dev& d, EvalSmem& sm, const volatile int* vbp, int cur, const WarpRec& rec) {
     using T = ModelTraits<MODEL>;
-    constexpr int L = T::L;
+    constexpr int L = T::L, ND = T::ND, S = kEvalStages;
     const int tid = tid_now();
     const int lane = tid & 31, warp = tid >> 5;
+    const int pair = warp & (kEvalPairs - 1);
+    const bool producer = warp < kEvalPairs;
+    EvalRing<MODEL>& ring = reinterpret_cast<EvalRing<MODEL>*>(dyn_smem)[pair];
+    unsigned long long* full = sm.full[pair];
+    unsigned long long* empty = sm.empty[pair];
     STAMP(d, 0, 0);
-    const double* P = d.Pbuf + (long long)cur * d.K;
-    const ViewC* const views[1] = {d.views + (long long)cur * d.M};
-    if (tid < L) sm.sc[tid] = P[tid];
+    if (tid < L) sm.sc[tid] = d.Pbuf[(long long)cur * d.K + tid];
+    if (tid < kEvalPairs * S) { mbar_init(&sm.full[0][0] + tid, 1); mbar_init(&sm.empty[0][0] + tid, 1); }
+    if (tid == 0) mbar_fence_init();
     __syncthreads();
-    // sweep 1: B_v, D_v, g_v -- one row of kNBD slots per piece
-    {
+    const int p0 = rec.p0, p1 = rec.p1;
+    if (producer) {
+        // ---- producer: projection chain, A / g_c / E, hand-off
+        double acc[kNA];
+#pragma unroll
+        for (int i = 0; i < kNA; ++i) acc[i] = 0.0;
+        double e = 0.0;
+        if (p0 < p1) {
+            const ViewC* views = d.views + (long long)cur * d.M;
+            Piece pc = rec.first;
+            Pt pn;
+            if (lane < pc.count) load_point(d, (long long)pc.start + lane, pn);
+            double vn = 0.0;
+            if (lane < kViewDoubles) vn = reinterpret_cast<const double*>(views + pc.view)[lane];
+            int k = 0;                                   // hand-offs so far
+            for (int pi = p0; pi < p1; ++pi) {
+                const bool has_next = pi + 1 < p1;
+                Piece nxt = pc;
+                if (has_next) nxt = d.ev_piece[pi + 1];
+                __syncwarp();
+                if (lane < kViewDoubles) reinterpret_cast<double*>(&sm.sview[pair])[lane] = vn;
+                __syncwarp();
+                if (has_next && lane < kViewDoubles) vn = reinterpret_cast<const double*>(views + nxt.view)[lane];
+                const int nsteps = (pc.count + 31) >> 5;
+                long long idx = (long long)pc.start + lane;
+                int left = pc.count - lane;              // > 0: this lane has a point in the current step
+                for (int sidx = 0; sidx < nsteps; ++sidx) {
+                    const Pt p = pn;
+                    const bool valid = left > 0;
+                    left -= 32;
+                    idx += 32;
+                    if (sidx + 1 < nsteps) { if (left > 0) load_point(d, idx, pn); }
+                    else if (has_next && lane < nxt.count) load_point(d, (long long)nxt.start + lane, pn);
+                    // the stage is normally free long before (the consumer has less to do per point)
+                    const int s = k % S;
+                    if (k >= S) mbar_wait_guarded(&empty[s], (unsigned)((k / S) - 1) & 1u, d.st, 0);
+                    PointOut<MODEL> o;
+                    if (valid) {
+                        point_eval<MODEL, true, true>(sm.sc, sm.sview[pair], p.X, p.Y, p.Z, p.U, p.V, o);
+                        double2* slot = &ring.v[s][0][lane];     // hand-off first: the extrinsic columns die here
+#pragma unroll
+                        for (int j = 0; j < 6; ++j) slot[(2 + ND + j) * 32] = make_double2(o.ju[j], o.jv[j]);
+                        slot[0 * 32] = make_double2(o.xd, o.yd);
+                        slot[1 * 32] = make_double2(o.ru, o.rv);
+#pragma unroll
+                        for (int a = 0; a < ND; ++a) slot[(2 + a) * 32] = make_double2(o.ku[a], o.kv[a]);
+                    }
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&full[s]);
+                    if (valid) accum_A<MODEL>(o, acc, e);
+                    ++k;
+                }
+                pc = nxt;
+            }
+        }
+        STAMP(d, 0, 1);
+        warp_reduce_scatter<kNA>(acc, lane);
+        e = warp_sum(e);
+        sm.sred[pair][2 * lane] = acc[0];
+        sm.sred[pair][2 * lane + 1] = acc[1];
+        if (lane == 0) sm.sE[pair] = e;
+    } else {
+        // ---- consumer: B_v, D_v, g_v -- one row of kNBD slots per piece
         double acc[kNBD];
 #pragma unroll
         for (int i = 0; i < kNBD; ++i) acc[i] = 0.0;
-        sweep_pieces<1, 1>(d, d.ev_piece, rec, views, sm.sview[warp], lane,
-            [&](const Piece&, int) {},
-            [&](const Pt& p) {
-                PointOut<MODEL> o;
-                point_eval<MODEL, true, true>(sm.sc, sm.sview[warp][0], p.X, p.Y, p.Z, p.U, p.V, o);
-                accum_BD<MODEL>(o, acc);
-            },
-            [&](const Piece&, int pi) {
+        if (p0 < p1) {
+            Piece pc = rec.first;
+            int k = 0;
+            for (int pi = p0; pi < p1; ++pi) {
+                const bool has_next = pi + 1 < p1;
+                Piece nxt = pc;
+                if (has_next) nxt = d.ev_piece[pi + 1];
+                const int nsteps = (pc.count + 31) >> 5;
+                int left = pc.count - lane;
+                for (int sidx = 0; sidx < nsteps; ++sidx) {
+                    const bool valid = left > 0;
+                    left -= 32;
+                    const int s = k % S;
+                    mbar_wait_guarded(&full[s], (unsigned)(k / S) & 1u, d.st, 1);
+                    if (valid) {
+                        accum_BD_ring<MODEL>(&ring.v[s][0][lane], acc);
+                    }
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&empty[s]);
+                    ++k;
+                }
                 warp_reduce_scatter<kNBD>(acc, lane);
                 double* row = d.partBD + (long long)pi * kNBD + lane * (kNBD / 32);
 #pragma unroll
                 for (int j = 0; j < kNBD / 32; ++j) row[j] = acc[j];
 #pragma unroll
                 for (int i = 0; i < kNBD; ++i) acc[i] = 0.0;
-            });
+                pc = nxt;
+            }
+        }
+        STAMP(d, 0, 2);
     }
-    STAMP(d, 0, 1);
-    // sweep 2: A, g_c, E -- accumulated over all pieces of the warp, one row per block.  The point
-    // loop runs on a step count and a running index (COUNTED): the piece's start and count are not
-    // live inside it, which removes its in-loop spill loads (profiles/README.md, static look at k_eval)
-    {
-        double acc[kNA];
-#pragma unroll
-        for (int i = 0; i < kNA; ++i) acc[i] = 0.0;
-        double e = 0.0;
-        sweep_pieces<1, 1, true>(d, d.ev_piece, rec, views, sm.sview[warp], lane,
-            [&](const Piece&, int) {},
-            [&](const Pt& p) {
-                PointOut<MODEL> o;
-                point_eval<MODEL, true, false>(sm.sc, sm.sview[warp][0], p.X, p.Y, p.Z, p.U, p.V, o);
-                accum_A<MODEL>(o, acc, e);
-            },
-            [&](const Piece&, int) {});
-        warp_reduce_scatter<kNA>(acc, lane);
-        e = warp_sum(e);
-        sm.sred[warp][2 * lane] = acc[0];
-        sm.sred[warp][2 * lane + 1] = acc[1];
-        if (lane == 0) sm.sE[warp] = e;
-    }
-    STAMP(d, 0, 2);
     __syncthreads();
     STAMP(d, 0, 3);
     const int vb = *vbp;
     if (tid < kNA) {
         double s = sm.sred[0][tid];
 #pragma unroll
-        for (int k = 1; k < kBlockWarps; ++k) s += sm.sred[k][tid];
+        for (int k = 1; k < kEvalPairs; ++k) s += sm.sred[k][tid];
         d.partA[(long long)vb * kNA + tid] = s;
     } else if (tid == kNA) {
         double s = sm.sE[0];
 #pragma unroll
-        for (int k = 1; k < kBlockWarps; ++k) s = __dadd_rn(s, sm.sE[k]);
+        for (int k = 1; k < kEvalPairs; ++k) s = __dadd_rn(s, sm.sE[k]);
         d.partE[vb] = s;
     }
     STAMP(d, 0, 4);
@@ -127,8 +238,8 @@ __device__ __forceinline__ void eval_block(const Dev& d, EvalSmem& sm, const vol
 
 template <int MODEL>
 __global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
-    const int warp = threadIdx.x >> 5;
-    const int w = blockIdx.x * kBlockWarps + warp;
+    const int pair = (threadIdx.x >> 5) & (kEvalPairs - 1);
+    const int w = blockIdx.x * kEvalPairs + pair;
     WarpRec rec;                       // issued together with the state load below: one round trip
     rec.p0 = rec.p1 = 0;
     pdl_trigger();
@@ -148,7 +259,10 @@ __global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
 // accepted one ends the pass, the rest is dropped.  st: the state to advance (the device state, or a
 // block's copy of it in the persistent kernel, where every block replays the same decisions from the
 // same trial costs and only one writes the trace).  Returns done.
-__device__ __forceinline__ int lm_accept_on(LmState* st, const double* etrial, double* trace) {
+// ptrace / Pcur (with trace, when st->want_ptrace): the L shared parameters of the current iterate go beside
+// every trace row -- what the reference prints per iteration (src/calibrate.py:158-159,269-274).
+__device__ __forceinline__ int lm_accept_on(LmState* st, const double* etrial, double* trace, double* ptrace = nullptr,
+                                            const double* Pcur = nullptr, int L = 0) {
     const int J = st->J, cur = st->cur;
     double lam = st->lam;
     const double E = st->E_cur;
@@ -160,6 +274,8 @@ __device__ __forceinline__ int lm_accept_on(LmState* st, const double* etrial, d
         if (trace) {
             double* tr = trace + 4ll * it;
             tr[0] = E; tr[1] = E1; tr[2] = lam; tr[3] = acc ? 1.0 : 0.0;
+            if (ptrace && st->want_ptrace)
+                for (int i = 0; i < L; ++i) ptrace[16ll * it + i] = Pcur[i];
         }
         if (acc) { st->cur = trial_buf(cur, j); lam = lam / 10.0; st->E_cur = E1; accepted = true; }
         else     { lam = lam * 10.0; }
@@ -184,7 +300,7 @@ __device__ __forceinline__ int lm_accept_on(LmState* st, const double* etrial, d
 // out of the plain variants: a kernel that calls the device runtime cannot be profiled by ncu.)
 template <bool COND>
 __device__ __forceinline__ void lm_accept(const Dev& d) {
-    const int done = lm_accept_on(d.st, d.etrial, d.trace);
+    const int done = lm_accept_on(d.st, d.etrial, d.trace, d.ptrace, d.Pbuf + (long long)d.st->cur * d.K, d.L);
     if (COND) cudaGraphSetConditional(d.cond, done ? 0u : 1u);
 }
 

@@ -19,11 +19,24 @@
 // Barriers per pass: [evaluation] - view stage - reduced solve - back-substitution - cost sweep.  One GPU:
 // every block sums the block costs itself (co_blocks x 4 doubles) and decides; sharded views: block 0
 // sums, exchanges with the peers, publishes the totals, and one more barrier follows.
+//
+// EXPERIMENT, not in the default build (-DCALIB_EXPERIMENT_PERSISTENT adds it as loop mode 3).  Measured on
+// B200 with the two-sweep evaluation pass of round 1 (profiles/r2b_persistent_first.txt,
+// r2c_pstamps_first.txt): bit-identical to loop modes 1 / 2, but NOT faster -- cfg1 28.1 against 27.1 us
+// per LM iteration, cfg3 1.61 against 1.21 ms per refinement.  A grid barrier (arrive + poll + two
+// gpu-scope fences) costs 1.5-2 us, what a kernel boundary inside the WHILE graph costs; the phases
+// themselves (view stage 3.6, reduced system 5.6, back-substitution 2.8 us at 540 points) are latency
+// chains that no launch mechanism shortens; the cost sweep loses a third with 8 instead of 16 warps per
+// SM, and ptxas spills inside the sweeps once they sit in one body with the other phases.  With the
+// producer / consumer evaluation pass of round 2 the hand-off of a chunk whose first step is a partial
+// warp never completes inside this kernel (the same code is fine as k_eval; not understood, the waits are
+// bounded so it fails with CALIB_E_CUDA instead of hanging).
 #pragma once
-#include "calib_solve.cuh"
+#include "../calib_solve.cuh"
 
 namespace calib {
 
+constexpr size_t kPersistDynSmem = kEvalDynSmem > kCostDynSmem ? kEvalDynSmem : kCostDynSmem;
 constexpr unsigned long long kGridTimeoutNs = 40ull * 1000 * 1000 * 1000;   // > the peer exchange's own timeout
 
 // Arrive-and-wait over all blocks of the (co-resident) grid.  `target` counts arrivals so far + one
@@ -113,7 +126,7 @@ __device__ __noinline__ void accept_phase(const Dev& d, CostSmem& sm, LmState& s
     cost_total(d, sm);                          // every block: same rows, same order, same sums
     if (tid_now() == 0) {
         if (blockIdx.x == 0) for (int j = 0; j < kJMax; ++j) d.etrial[j] = sm.s_tot[j];
-        lm_accept_on(&st, sm.s_tot, blockIdx.x == 0 ? d.trace : nullptr);
+        lm_accept_on(&st, sm.s_tot, blockIdx.x == 0 ? d.trace : nullptr, d.ptrace, d.Pbuf + (long long)st.cur * d.K, d.L);
     }
 }
 
@@ -131,7 +144,7 @@ __device__ __noinline__ void accept_published_phase(const Dev& d, LmState& st) {
     if (tid_now() == 0) {
         double et[kJMax];
         for (int j = 0; j < kJMax; ++j) et[j] = __ldcg(d.etrial + j);
-        lm_accept_on(&st, et, blockIdx.x == 0 ? d.trace : nullptr);
+        lm_accept_on(&st, et, blockIdx.x == 0 ? d.trace : nullptr, d.ptrace, d.Pbuf + (long long)st.cur * d.K, d.L);
     }
 }
 
@@ -161,7 +174,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) k_lm_persistent(const __grid
             if (tid_now() == 0) s_vb = blockIdx.x;
             __syncthreads();
             while (s_vb < d.ev_blocks) {
-                const int w = s_vb * kBlockWarps + (tid_now() >> 5);
+                const int w = s_vb * kEvalPairs + ((tid_now() >> 5) & (kEvalPairs - 1));
                 WarpRec rec;
                 rec.p0 = rec.p1 = 0;
                 if (w < d.ev_warps) rec = d.ev_rec[w];

@@ -142,6 +142,12 @@ int calib_lm_run_resident(calib_t* h, int maxIters, double lam0, double lam_min,
                           double err_min, double* sse_out, int* iters_out);
 int calib_download_params(calib_t* h, double* P);
 int calib_download_trace(calib_t* h, int iters, double* trace);
+/* What the reference prints per iteration when shouldPrint is set (src/calibrate.py:158-159, 269-274):
+ * A and k of the iterate BEFORE the update.  calib_set_param_trace(h, 1): the runs that follow record the
+ * L shared parameters (alpha, beta, gamma, uc, vc, k...) of the iterate each trace row started from (written
+ * by the accept step: no extra launch); calib_download_param_trace: out = iters x L. */
+int calib_set_param_trace(calib_t* h, int on);
+int calib_download_param_trace(calib_t* h, int iters, double* out);
 
 /* Device time of the last calib_lm_run* (CUDA events on the handle's stream), and the number
  * of kernels it launched.  Per-kernel timing: calib_set_profiling(h,1) brackets every launch of
@@ -231,6 +237,36 @@ int calib_peer_attach(calib_t* h, int nranks, int rank, const void* handles);
 /* 0 = automatic (peer memory when attached, else NCCL), 1 = NCCL, 2 = peer memory. */
 int calib_set_transport(calib_t* h, int mode);
 int calib_transport(const calib_t* h);   /* in use: 0 none (one GPU), 1 NCCL, 2 peer memory */
+
+/* ONE process, SEVERAL GPUs: what the reference's boundary needs to use more than one device, since its
+ * call is one synchronous method of one Python process (Calibrator.refineCalibrationParameters,
+ * src/calibrate.py:117-118; main.calibrateCamera, src/main.py:34-35).  The library shards the views over
+ * device_ids[0 .. n_gpus) (contiguous ranges balanced by point count; never more devices than views), keeps
+ * one ordinary handle per device -- created by one host thread each, so the uploads use all the PCIe links
+ * at once -- and joins them with the in-kernel exchange described above: the peers' inboxes are reached
+ * through cudaDeviceEnablePeerAccess (one address space; no IPC handles, no torch, no launcher).  The
+ * caller passes and gets back ONE full-length parameter vector (K = L + 6 M); results are those of the
+ * one-process-per-GPU path, bit for bit.  calib_multi_lm_run: arguments of calib_lm_run plus device_ms
+ * (nullable: device time of the slowest rank, CUDA events).  One host thread enqueues every device's
+ * whole-loop launch, then waits for all of them.  The devices must be peer-accessible (NVLink / NVSwitch). */
+typedef struct calib_multi_handle calib_multi_t;
+int calib_multi_create(calib_multi_t** out, int model, int64_t M, const int64_t* view_offsets,
+                       const double* model_pts, const double* sensor_pts, int n_gpus, const int* device_ids);
+int calib_multi_create_from_views(calib_multi_t** out, int model, int64_t M, const int64_t* counts,
+                                  const double* const* model_ptrs, const double* const* sensor_ptrs,
+                                  int n_gpus, const int* device_ids);
+void calib_multi_destroy(calib_multi_t* h);
+const char* calib_multi_last_error(const calib_multi_t* h);
+int calib_multi_num_gpus(const calib_multi_t* h);        /* devices in use (<= n_gpus asked for) */
+int64_t calib_multi_num_params(const calib_multi_t* h);  /* K = L + 6M */
+int calib_multi_view_bounds(const calib_multi_t* h, int64_t* bounds /* num_gpus + 1 */);
+int calib_multi_set_loop_mode(calib_multi_t* h, int mode);   /* 0 auto, 2 WHILE graph */
+int calib_multi_set_ladder(calib_multi_t* h, int max_candidates);
+int calib_multi_set_param_trace(calib_multi_t* h, int on);
+int calib_multi_download_param_trace(calib_multi_t* h, int iters, double* out);
+int calib_multi_lm_run(calib_multi_t* h, double* P_inout, int maxIters, double lam0, double lam_min,
+                       double lam_max, double err_min, double* sse_out, int* iters_out, double* trace,
+                       double* device_ms);
 
 /* Batch of independent calibrations (a Python `for` over refineCalibrationParameters calls in the
  * reference; BASELINE config 4): one thread block per problem, the whole LM loop in one launch,

@@ -69,6 +69,15 @@ def main():
         rel = float((d / np.maximum(np.abs(P1), 1e-3)).max())
         if rel > 1e-6 or abs(sse - s1) > 1e-9 * s1:
             ok, msg = False, f"parameters differ: {rel}"
+        # the single-process handle over the same devices (calib_multi_*: library-side sharding, peer access
+        # instead of IPC handles) must repeat the one-process-per-GPU result bit for bit
+        if transport == "peer":
+            mprob = cc.MultiProblem(model, offs_a, mp_a, sp_a, devices=list(range(world)))
+            mprob.set_loop_mode(2 if loop_mode == 2 else 0)
+            sm, Pm, im, tm = mprob.lm_run(P0, 100)
+            mprob.close()
+            if not (im == iters and sm == sse and np.array_equal(tm, tr) and np.array_equal(Pm, Pfull)):
+                ok, msg = False, "single-process multi-device handle differs from the one-process-per-GPU path"
         print(json.dumps({"ok": ok, "msg": msg, "world": world, "iters_sharded": iters, "iters_single": i1,
                           "pre_plateau_iterations": int(stop), "max_rel_param_diff": rel,
                           "transport": used, "launches": int(launches)}), flush=True)

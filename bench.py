@@ -202,7 +202,9 @@ def parity_block(P, sse, it, tr, Pr, sser, itr, trr, other):
     scale[2] = max(scale[2], abs(Pr[0]))            # the skew is measured at the scale of alpha (tests/conftest.py)
     rel = float((d / scale).max())
     sse_rel = float(abs(sse - sser) / abs(sser)) if sser else float(abs(sse - sser))
-    ok = bool(same and cost_rel <= 1e-9 and rel <= 1e-6 and sse_rel <= 1e-9)
+    # parameters: 1e-5 -- the two runs stop at different points of the flat valley past the cost plateau (their
+    # post-plateau iteration counts differ, see iters / iters_*); up to the plateau they are the same run
+    ok = bool(same and cost_rel <= 1e-9 and rel <= 1e-5 and sse_rel <= 1e-9)
     return {"ok": ok, "against": other, "pre_plateau_trace_equal": same, "pre_plateau_iterations": int(stop),
             "pre_plateau_cost_max_rel_diff": cost_rel, "max_rel_param_diff": rel, "sse_rel_diff": sse_rel,
             "iters": int(it), "iters_" + ("oracle" if "oracle" in other else "single"): int(itr)}
@@ -532,6 +534,42 @@ def bench_calibration(args, env, name, scale, steps, warmup, light=False):
                "ms_per_refinement": 1e3 * dt / n_e2e, "steps": n_e2e,
                "api": "C-ABI per step" + (" and rank" if world > 1 else "") +
                       ": calib_create(page-locked CSR host buffers) + calib_lm_run(host P) + calib_destroy"}
+        if world > 1:
+            # the drop-in's own way to several GPUs: ONE process (rank 0's), the library shards the views and
+            # drives all N devices (calib_multi_*); the other ranks' processes sit at the barrier meanwhile
+            sp_block = None
+            env["cpu_barrier"]()
+            if rank == 0:
+                offs_a, mp_a, sp_a = flatten_np(c["dets"])
+                mpa, mpa_ptr = pinned_copy(lib, mp_a)
+                spa, spa_ptr = pinned_copy(lib, sp_a)
+
+                def sp_step():
+                    mprob = cc.MultiProblem(model, offs_a, mpa, spa, list(range(world)))
+                    mprob.set_ladder(args.ladder)
+                    _, _, it, _ = mprob.lm_run(P0, MAX_ITERS, want_trace=False)
+                    ms = mprob.last_device_ms
+                    mprob.close()
+                    return it, ms
+                for _ in range(2):
+                    sp_step()
+                n_sp = max(3, min(steps, 20))
+                t0 = time.perf_counter()
+                it_sp = ms_sp = 0
+                for _ in range(n_sp):
+                    it, ms = sp_step()
+                    it_sp += it
+                    ms_sp += ms
+                dts = time.perf_counter() - t0
+                lib.calib_host_free(mpa_ptr)
+                lib.calib_host_free(spa_ptr)
+                sp_block = {"value": it_sp / dts, "unit": "LM iterations/s", "ms_per_refinement": 1e3 * dts / n_sp,
+                            "device_ms_per_refinement": ms_sp / n_sp, "steps": n_sp,
+                            "h2d_bytes_per_step": int(40 * offs_a[-1] + 8 * len(P0)), "d2h_bytes_per_step": int(8 * len(P0)),
+                            "api": "ONE process: calib_multi_create(page-locked CSR host buffers, all N devices) + "
+                                   "calib_multi_lm_run(full-length host P) + calib_multi_destroy"}
+            env["cpu_barrier"]()
+            e2e["single_process"] = sp_block
         if world == 1:
             cal = cc.Calibrator(model, device=local)
             A0, W0, k0 = cal._decomposeParameterVector(P0)
@@ -691,9 +729,11 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dist = None
+    cpu_group = None
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        cpu_group = dist.new_group(backend="gloo")      # host-side waits that leave the GPUs idle (see cpu_barrier)
 
     def barrier():
         torch.cuda.synchronize()
@@ -701,7 +741,15 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
-    env = {"rank": rank, "world": world, "local": local, "dist": dist, "barrier": barrier}
+    def cpu_barrier():
+        """A barrier that does NOT run on the GPUs: while rank 0's process drives every device by itself (single-
+        process handle, one-GPU parity run) the other ranks must not sit in an NCCL barrier -- its kernel would
+        spin on their GPU and time-slice with rank 0's kernels there."""
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier(group=cpu_group)
+
+    env = {"rank": rank, "world": world, "local": local, "dist": dist, "barrier": barrier, "cpu_barrier": cpu_barrier}
     if args.workload == "cfg4":
         line = bench_batch(args, env, 10 if args.steps == 100 else args.steps)
         if rank == 0:
@@ -742,7 +790,7 @@ def run_calibration_with_parity(args, env, name, scale, steps, warmup, light):
     if world > 1:
         # rank 0 alone runs the whole workload on its one GPU (the communicator is not lent to this handle)
         prob.comm_set_default(local, on=False)
-        env["barrier"]()
+        env["cpu_barrier"]()
         if rank == 0:
             model = c["model"]
             L = 10 if model == 0 else 9
@@ -758,7 +806,7 @@ def run_calibration_with_parity(args, env, name, scale, steps, warmup, light):
             parity["ranks_agree"] = sh["agree"]
             parity["ok"] = bool(parity["ok"] and sh["agree"])
             parity["single_gpu_ms_per_refinement"] = ms1
-        env["barrier"]()
+        env["cpu_barrier"]()
     if rank == 0 and parity_key and parity is not None:
         line[parity_key] = parity
     prob.close()

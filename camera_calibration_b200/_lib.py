@@ -107,6 +107,7 @@ def lib():
         "calib_download_trace": (c_int, [_vp, c_int, _d]),
         "calib_set_param_trace": (c_int, [_vp, c_int]),
         "calib_download_param_trace": (c_int, [_vp, c_int, _d]),
+        "calib_multi_flush_l2": (c_int, [_vp]),
         "calib_multi_set_param_trace": (c_int, [_vp, c_int]),
         "calib_multi_download_param_trace": (c_int, [_vp, c_int, _d]),
         "calib_last_run_stats": (c_int, [_vp, _d, _i64, _i64]),

@@ -479,6 +479,9 @@ class MultiProblem:
         self.last_device_ms = ms.value
         return sse.value, P, iters.value, (trace[:iters.value].copy() if want_trace else None)
 
+    def flush_l2(self):
+        self._check(self._L.calib_multi_flush_l2(self._h))
+
     def set_param_trace(self, on):
         self._check(self._L.calib_multi_set_param_trace(self._h, 1 if on else 0))
 

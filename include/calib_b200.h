@@ -94,7 +94,8 @@ int calib_set_pdl(calib_t* h, int on);
 
 /* How the trial-cost sweep brings the detections in: 1 = bulk copies (TMA) into a per-warp
  * shared-memory ring, 0 = coalesced loads with register prefetch, -1 (default) = by size (the ring
- * when the detections exceed what L2 keeps between sweeps).  Results are bit-identical. */
+ * when the detections exceed what L2 keeps between sweeps).  Same points, same code; a lane's share of a
+ * warp's chunk differs between the two, so the costs agree to rounding (1e-13), not bit for bit. */
 int calib_set_cost_staging(calib_t* h, int mode);
 
 /* Page-locked host memory for detections / parameters handed to calib_create / calib_lm_run
@@ -262,6 +263,7 @@ int64_t calib_multi_num_params(const calib_multi_t* h);  /* K = L + 6M */
 int calib_multi_view_bounds(const calib_multi_t* h, int64_t* bounds /* num_gpus + 1 */);
 int calib_multi_set_loop_mode(calib_multi_t* h, int mode);   /* 0 auto, 2 WHILE graph */
 int calib_multi_set_ladder(calib_multi_t* h, int max_candidates);
+int calib_multi_flush_l2(calib_multi_t* h);                  /* calib_flush_l2 on every device */
 int calib_multi_set_param_trace(calib_multi_t* h, int on);
 int calib_multi_download_param_trace(calib_multi_t* h, int iters, double* out);
 int calib_multi_lm_run(calib_multi_t* h, double* P_inout, int maxIters, double lam0, double lam_min,

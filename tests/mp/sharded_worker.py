@@ -18,6 +18,7 @@ def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    cpu = dist.new_group(backend="gloo")     # waits that leave the GPUs idle while rank 0 drives all of them alone
     name, scale, loop_mode = sys.argv[1], float(sys.argv[2]), int(sys.argv[3])
     c = synth.config(name, scale)
     model = c["model"]
@@ -46,7 +47,8 @@ def main():
     prob.comm_set_default(local, on=False)
     # gather the extrinsics of every rank on rank 0
     parts = [None] * world
-    dist.all_gather_object(parts, (lo, hi, P.tolist(), sse, iters, tr.tolist()))
+    dist.all_gather_object(parts, (lo, hi, P.tolist(), sse, iters, tr.tolist()), group=cpu)
+    torch.cuda.synchronize()
     ok, msg = True, ""
     if rank == 0:
         Pfull = sharding.merge_params([(a, b, np.array(p)) for a, b, p, *_ in parts], L, len(c["dets"]))
@@ -81,7 +83,8 @@ def main():
         print(json.dumps({"ok": ok, "msg": msg, "world": world, "iters_sharded": iters, "iters_single": i1,
                           "pre_plateau_iterations": int(stop), "max_rel_param_diff": rel,
                           "transport": used, "launches": int(launches)}), flush=True)
-    dist.barrier()      # nobody unmaps an inbox a peer may still write to
+    dist.barrier(group=cpu)      # nobody unmaps an inbox a peer may still write to (host-side barrier: rank 0 may
+                                 # still be running on every GPU through the single-process handle)
     prob.close()
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)

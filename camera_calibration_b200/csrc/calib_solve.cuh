@@ -423,13 +423,14 @@ __device__ __forceinline__ void backsub_block(const Dev& d, BacksubSmem& sm, int
                 double s = x[i];
 #pragma unroll
                 for (int k = i + 1; k < 6; ++k) s = fma(-Lc[k * (k + 1) / 2 + i], x[k], s);
-                x[i] = s * Lc[i * (i + 1) / 2 + i];      // the diagonal slot holds 1 / L_ii
+                x[i] = __dmul_rn(s, Lc[i * (i + 1) / 2 + i]);      // the diagonal slot holds 1 / L_ii (explicit roundings,
+                                                                   // as in backsub_thread: the two must agree bit for bit)
             }
             double e[6];
 #pragma unroll
             for (int i = 0; i < 6; ++i) {
                 const long long idx = L + 6ll * v + i;
-                e[i] = P[idx] + x[i];
+                e[i] = __dadd_rn(P[idx], x[i]);
                 Pt[idx] = e[i];
                 if (j == 0) d.delta[idx] = x[i];
             }

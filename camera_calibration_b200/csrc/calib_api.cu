@@ -73,6 +73,7 @@ struct calib_handle {
     cudaStream_t stream = nullptr;
     cudaGraphExec_t graph = nullptr;       // one iteration (host-driven loop)
     cudaGraphExec_t loop_graph = nullptr;  // WHILE node around the iteration (device-driven loop)
+    struct CachedLoop* loop = nullptr;     // its source graph, nodes and key: parked for the next handle of that shape
     int loop_mode = 0;                     // 0 auto, 1 host-driven, 2 device WHILE graph, 3 persistent kernel
     int persist_blocks = 0;                // co-resident blocks of the persistent kernel on this device (0: not asked yet)
     int cost_tma = -1;                     // -1 auto (by size), 0 plain loads, 1 bulk-copy ring
@@ -237,51 +238,77 @@ static void ctx_release(calib_handle* h) {
     h->stream = nullptr; h->ev0 = h->ev1 = nullptr; h->h_state = nullptr; h->h_pinned = nullptr;
 }
 
-static void drop_graph(calib_handle* h) {
-    if (h->graph) { cudaGraphExecDestroy(h->graph); h->graph = nullptr; }
-    if (h->loop_graph) { cudaGraphExecDestroy(h->loop_graph); h->loop_graph = nullptr; }
-}
-
-// Tearing down an instantiated loop graph costs ~0.12 ms of host time, as much as everything else in
-// calib_destroy together times ten.  A destroyed handle parks its graphs here; the next calib_create on
-// that device destroys them while its detections cross PCIe (nothing else to do on the host then).  At
-// most kTrashMax graphs wait; beyond that the oldest are destroyed on the spot.
-struct TrashedGraph { int device; cudaGraphExec_t exec; };
-static std::mutex g_trash_mu;
-static std::vector<TrashedGraph> g_trash;
-constexpr size_t kTrashMax = 8;
-
-static void empty_trash(int device, size_t keep) {   // device < 0: any
-    std::vector<TrashedGraph> doomed;
-    {
-        std::lock_guard<std::mutex> lk(g_trash_mu);
-        std::vector<TrashedGraph> rest;
-        size_t excess = g_trash.size() > keep ? g_trash.size() - keep : 0;
-        for (const TrashedGraph& t : g_trash) {
-            if (excess && (device < 0 || t.device == device)) { doomed.push_back(t); --excess; }
-            else rest.push_back(t);
-        }
-        g_trash.swap(rest);
+// An instantiated WHILE-loop graph is expensive to make (capture + instantiate: 0.3-0.5 ms of host time, and
+// the driver serialises it across the host threads of a process) but depends on the problem only through the
+// kernels' by-value argument (Dev: pointers, sizes) and the grid sizes.  So a handle that lets go of its loop
+// graph parks it here -- source graph, executable graph, the kernel nodes of the WHILE body -- and the next
+// handle on that device whose iteration has the same shape (model, grid sizes, cost-pass variant) takes it
+// and re-points the nodes at its own Dev with cudaGraphExecKernelNodeSetParams: a few microseconds
+// (profiles/r2q_graph_patch.txt: 4 us against 540 us).  At most kLoopCacheMax graphs wait per process; the
+// oldest beyond that are destroyed when the next handle is created (under its upload).
+struct LoopKey {
+    int device, model, ev_blocks, co_blocks, sc_groups, bs_groups, tma, pdl;
+    bool operator==(const LoopKey& o) const {
+        return device == o.device && model == o.model && ev_blocks == o.ev_blocks && co_blocks == o.co_blocks &&
+               sc_groups == o.sc_groups && bs_groups == o.bs_groups && tma == o.tma && pdl == o.pdl;
     }
-    if (doomed.empty()) return;
+};
+struct CachedLoop {
+    LoopKey key;
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    cudaGraphConditionalHandle cond{};
+    struct Node { cudaGraphNode_t node; cudaKernelNodeParams kp; int n_int; int iarg[2]; };
+    std::vector<Node> nodes;               // kernel nodes of the WHILE body
+};
+static std::mutex g_loop_mu;
+static std::vector<CachedLoop*> g_loop_cache;
+constexpr size_t kLoopCacheMax = 16;
+
+static void destroy_loop(CachedLoop* c) {
+    if (!c) return;
     int cur = 0;
     cudaGetDevice(&cur);
-    for (const TrashedGraph& t : doomed) {
-        if (t.device != cur) cudaSetDevice(cur = t.device);
-        cudaGraphExecDestroy(t.exec);
-    }
+    if (cur != c->key.device) cudaSetDevice(c->key.device);
+    if (c->exec) cudaGraphExecDestroy(c->exec);
+    if (c->graph) cudaGraphDestroy(c->graph);
+    if (cur != c->key.device) cudaSetDevice(cur);
+    delete c;
 }
 
-static void park_graphs(calib_handle* h) {
+// hands the handle's loop graph to the cache (destroy = true: a handle that holds an NCCL communicator must
+// tear its graphs down at once; such graphs are never cached anyway)
+static void park_loop(calib_handle* h, bool destroy = false) {
+    CachedLoop* c = h->loop;
+    h->loop = nullptr; h->loop_graph = nullptr;
+    if (!c) return;
+    if (destroy) { destroy_loop(c); return; }
+    std::lock_guard<std::mutex> lk(g_loop_mu);
+    g_loop_cache.push_back(c);
+}
+
+// destroys the oldest parked graphs beyond `keep` (called where host time is free: under an upload)
+static void trim_loop_cache(size_t keep) {
+    std::vector<CachedLoop*> doomed;
     {
-        std::lock_guard<std::mutex> lk(g_trash_mu);
-        if (h->graph) g_trash.push_back({h->device, h->graph});
-        if (h->loop_graph) g_trash.push_back({h->device, h->loop_graph});
+        std::lock_guard<std::mutex> lk(g_loop_mu);
+        while (g_loop_cache.size() > keep) { doomed.push_back(g_loop_cache.front()); g_loop_cache.erase(g_loop_cache.begin()); }
     }
-    h->graph = nullptr; h->loop_graph = nullptr;
-    const int dev = h->device;
-    empty_trash(-1, kTrashMax);
-    cudaSetDevice(dev);
+    for (CachedLoop* c : doomed) destroy_loop(c);
+}
+
+static void drop_graph(calib_handle* h) {
+    if (h->graph) { cudaGraphExecDestroy(h->graph); h->graph = nullptr; }
+    park_loop(h);
+}
+
+static void empty_trash(int, size_t) { trim_loop_cache(kLoopCacheMax); }
+
+static void park_graphs(calib_handle* h) {
+    if (h->graph) { cudaGraphExecDestroy(h->graph); h->graph = nullptr; }
+    park_loop(h);
+    trim_loop_cache(2 * kLoopCacheMax);
+    cudaSetDevice(h->device);
 }
 
 // Cuts the N points into n_warps contiguous, near-equal chunks (one per persistent warp) and each
@@ -706,7 +733,7 @@ extern "C" void calib_destroy(calib_t* h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     // The graphs are destroyed by the next calib_create, under its upload -- unless they hold NCCL nodes:
     // ncclCommDestroy waits for every graph that captured its collectives, so those go first, now.
-    if (h->comm) drop_graph(h);
+    if (h->comm) { if (h->graph) { cudaGraphExecDestroy(h->graph); h->graph = nullptr; } park_loop(h, true); }
     else park_graphs(h);
     if (h->comm && h->comm_owned && g_nccl.ok) g_nccl.CommDestroy(h->comm);
     for (auto& pe : h->prof_events) { cudaEventDestroy(pe.second.first); cudaEventDestroy(pe.second.second); }
@@ -991,6 +1018,39 @@ int build_graph(calib_handle* h) {
 int build_loop_graph(calib_handle* h) {
     if (h->loop_graph) return CALIB_OK;
     ScopeTimer tm_("build_loop_graph");
+    const Dev& d0 = h->dev;
+    const LoopKey key{h->device, h->model, d0.ev_blocks, d0.co_blocks, d0.sc_groups, d0.bs_groups,
+                      cost_uses_tma(h) ? 1 : 0, (h->pdl != 0 && !nccl_active(h)) ? 1 : 0};
+    const bool cacheable = !nccl_active(h);
+    if (cacheable) {
+        CachedLoop* c = nullptr;
+        {
+            std::lock_guard<std::mutex> lk(g_loop_mu);
+            for (size_t i = g_loop_cache.size(); i-- > 0;)
+                if (g_loop_cache[i]->key == key) { c = g_loop_cache[i]; g_loop_cache.erase(g_loop_cache.begin() + i); break; }
+        }
+        if (c) {
+            // same shape: re-point the kernel nodes of the WHILE body at this handle's Dev
+            h->dev.cond = c->cond;
+            Dev dcopy = h->dev;
+            dcopy.use_cond = 1;
+            cudaError_t e = cudaSuccess;
+            for (CachedLoop::Node& n : c->nodes) {
+                void* args[3] = {&dcopy, &n.iarg[0], &n.iarg[1]};
+                cudaKernelNodeParams kp = n.kp;
+                kp.kernelParams = args;
+                kp.extra = nullptr;
+                e = cudaGraphExecKernelNodeSetParams(c->exec, n.node, &kp);
+                if (e != cudaSuccess) break;
+            }
+            if (e == cudaSuccess) {
+                h->loop = c; h->loop_graph = c->exec;
+                return CALIB_OK;
+            }
+            cudaGetLastError();
+            destroy_loop(c);             // could not be re-pointed: build a fresh one below
+        }
+    }
     cudaGraph_t g = nullptr;
     CUDA_TRY(h, cudaGraphCreate(&g, 0));
     cudaGraphConditionalHandle handle;
@@ -1018,9 +1078,40 @@ int build_loop_graph(calib_handle* h) {
     h->dev.use_cond = 0;
     if (rc) { cudaGraphDestroy(g); return rc; }
     if (e != cudaSuccess) { cudaGraphDestroy(g); CUDA_TRY(h, e); }
-    e = cudaGraphInstantiate(&h->loop_graph, g, 0);
-    cudaGraphDestroy(g);
-    CUDA_TRY(h, e);
+    cudaGraphExec_t exec = nullptr;
+    e = cudaGraphInstantiate(&exec, g, 0);
+    if (e != cudaSuccess) { cudaGraphDestroy(g); CUDA_TRY(h, e); }
+    CachedLoop* c = new CachedLoop();
+    c->key = key; c->graph = g; c->exec = exec; c->cond = handle;
+    if (cacheable) {
+        // the kernel nodes of the body with their launch geometry and trailing int arguments (k_schur: fuse_solve,
+        // k_cost: fuse_accept); a graph whose nodes cannot be read is simply not reusable
+        size_t n = 0;
+        bool ok = cudaGraphGetNodes(body, nullptr, &n) == cudaSuccess && n > 0;
+        std::vector<cudaGraphNode_t> nodes(n);
+        ok = ok && cudaGraphGetNodes(body, nodes.data(), &n) == cudaSuccess;
+        for (size_t i = 0; ok && i < n; ++i) {
+            cudaGraphNodeType ty;
+            if (cudaGraphNodeGetType(nodes[i], &ty) != cudaSuccess) { ok = false; break; }
+            if (ty != cudaGraphNodeTypeKernel) continue;
+            CachedLoop::Node cn{};
+            cn.node = nodes[i];
+            if (cudaGraphKernelNodeGetParams(nodes[i], &cn.kp) != cudaSuccess) { ok = false; break; }
+            const void* f = cn.kp.func;
+            const bool is_schur = f == (const void*)k_schur<0> || f == (const void*)k_schur<1>;
+            const bool is_cost = f == (const void*)k_cost<0, true, false> || f == (const void*)k_cost<0, true, true> ||
+                                 f == (const void*)k_cost<1, true, false> || f == (const void*)k_cost<1, true, true>;
+            cn.n_int = (is_schur || is_cost) ? 1 : 0;
+            cn.iarg[0] = cn.n_int ? *(const int*)cn.kp.kernelParams[1] : 0;
+            cn.iarg[1] = 0;
+            cn.kp.kernelParams = nullptr;
+            c->nodes.push_back(cn);
+        }
+        if (!ok) { cudaGetLastError(); c->nodes.clear(); c->key.device = -1; }    // never matches a lookup
+    } else {
+        c->key.device = -1;
+    }
+    h->loop = c; h->loop_graph = exec;
     return CALIB_OK;
 }
 

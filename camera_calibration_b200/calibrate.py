@@ -245,6 +245,10 @@ class Problem:
         """damping ladder: trial steps taken ahead of the accept/reject decisions (1 = off, 2, 4)"""
         self._check(self._L.calib_set_ladder(self._h, int(max_candidates)))
 
+    def set_ladder_start(self, candidates):
+        """candidates of the pass that follows an accepted step (1, 2, or 0 = adaptive, the default)"""
+        self._check(self._L.calib_set_ladder_start(self._h, int(candidates)))
+
     def set_pdl(self, on):
         self._check(self._L.calib_set_pdl(self._h, 1 if on else 0))
 

@@ -99,6 +99,7 @@ struct calib_handle {
     int pdl = 0;                           // programmatic dependent launch between the kernels of the iteration (measured: no gain, off)
     bool pdl_now = false;                  // set while the iteration is being captured into a graph
     int ladder = kJMax;                    // cap of the damping ladder (1 = one candidate per pass)
+    int ladder_start = 0;                  // candidates of the pass that follows an accepted step: 1, 2, 0 = adaptive
     int transport = 0;                     // 0 auto (peer memory when attached, else NCCL), 1 NCCL, 2 peer memory
     double* l2buf = nullptr;
     size_t l2bytes = 0;
@@ -783,6 +784,13 @@ extern "C" int calib_set_ladder(calib_t* h, int max_candidates) {
     return CALIB_OK;
 }
 
+extern "C" int calib_set_ladder_start(calib_t* h, int candidates) {
+    if (!h) return fail(nullptr, CALIB_E_ARG, "NULL handle");
+    if (candidates < 0 || candidates > 2) return fail(h, CALIB_E_ARG, "calib_set_ladder_start: 0 (adaptive), 1 or 2 candidates");
+    h->ladder_start = candidates;
+    return CALIB_OK;
+}
+
 extern "C" int calib_set_cost_staging(calib_t* h, int mode) {
     if (!h) return fail(nullptr, CALIB_E_ARG, "NULL handle");
     if (mode < -1 || mode > 1) return fail(h, CALIB_E_ARG, "calib_set_cost_staging: -1 auto, 0 loads, 1 bulk copies");
@@ -1127,6 +1135,8 @@ int push_state(calib_handle* h, double lam, double lam_min, double lam_max, doub
     s.lam = lam; s.lam_min = lam_min; s.lam_max = lam_max; s.err_min = err_min;
     s.max_iters = max_iters; s.need_eval = 1; s.cur = h->cur; s.nranks = h->nranks;
     s.J = 1; s.jmax = std::max(1, std::min(jmax, (int)kJMax));
+    s.jstart = std::min(h->ladder_start, s.jmax);      // 0: adaptive
+    s.jdyn = 1;
     s.want_ptrace = h->want_ptrace ? 1 : 0;
     *h->h_state = s;
     CUDA_TRY(h, cudaMemcpyAsync(h->dev.st, h->h_state, sizeof(LmState), cudaMemcpyHostToDevice, h->stream));

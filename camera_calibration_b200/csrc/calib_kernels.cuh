@@ -52,6 +52,8 @@ struct LmState {
     int iter, max_iters, done, need_eval, cur, nranks;
     int comm_fail;         // a peer never arrived at an exchange (calib_peer.cuh)
     int J, jmax;           // candidates of this pass of the damping ladder; its cap (1 = ladder off)
+    int jstart;            // candidates of the pass after an ACCEPTED step: 1, 2, or 0 = adaptive (see lm_accept_on)
+    int jdyn;              // adaptive: 2 while the step tried right after an accepted one keeps being rejected, else 1
     int n_pass;            // passes (one k_schur/k_backsub/k_cost each) so far
     unsigned int cnt_schur, cnt_cost, cnt_eval, pad1;
     long long n_eval;   // Jacobian evaluations actually executed

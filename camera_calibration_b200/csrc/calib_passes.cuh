@@ -268,9 +268,11 @@ __device__ __forceinline__ int lm_accept_on(LmState* st, const double* etrial, d
     const double E = st->E_cur;
     int it = st->iter, done = 0;
     bool accepted = false;
+    const bool after_accept = st->need_eval != 0 && it > 0;     // this pass tries the step right after an accepted one
     for (int j = 0; j < J && !done && !accepted; ++j) {
         const double E1 = etrial[j];
         const bool acc = E1 < E;   // strict; NaN rejects
+        if (j == 0 && after_accept) st->jdyn = acc ? 1 : 2;
         if (trace) {
             double* tr = trace + 4ll * it;
             tr[0] = E; tr[1] = E1; tr[2] = lam; tr[3] = acc ? 1.0 : 0.0;
@@ -288,7 +290,14 @@ __device__ __forceinline__ int lm_accept_on(LmState* st, const double* etrial, d
     st->sse = E;
     st->iter = it;
     st->n_pass += 1;
-    int nj = accepted ? 1 : 2 * J;
+    // Candidates of the next pass: after rejections the ladder doubles; after an ACCEPTED step it starts at 1 or
+    // 2.  LM runs bounce -- an accepted step divides lambda by 10 and the step tried next is often rejected and
+    // retried at 10 lambda (itest: 35 of 44 accepted steps, cfg1: 9 of 16, cfg3: 3 of 8, cfg2: none) -- and with two
+    // candidates the pass after an accept already carries the retry: one pass (schur + back-substitution + cost,
+    // ~36 us) less per bounce for ~5 us of extra arithmetic in the cost sweep when there is none.  jstart = 0
+    // (default) predicts from the last time: 2 while the step after an accepted one keeps being rejected, else 1.
+    // Which candidates a pass carries never changes a result (test_damping_ladder_is_invisible).
+    int nj = accepted ? (st->jstart ? st->jstart : st->jdyn) : 2 * J;
     if (nj > st->jmax) nj = st->jmax;
     if (nj > st->max_iters - it) nj = st->max_iters - it;
     st->J = nj < 1 ? 1 : nj;

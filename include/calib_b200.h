@@ -86,6 +86,10 @@ int calib_set_loop_mode(calib_t* h, int mode);
  * candidate by candidate.  Iterates, costs, lambdas, trace rows and the iteration count are those of
  * the one-at-a-time loop, bit for bit; only the number of launches changes.  1, 2 or 4 (default 4). */
 int calib_set_ladder(calib_t* h, int max_candidates);
+/* Candidates of the pass that follows an ACCEPTED step: 1; 2 (the retry at 10 lambda rides along: LM runs
+ * bounce, the step tried right after an accepted one is often rejected); 0 (default) = adaptive, 2 while that
+ * keeps happening, else 1.  Bit-identical results. */
+int calib_set_ladder_start(calib_t* h, int candidates);
 
 /* Programmatic dependent launch between the kernels of the iteration inside the captured graphs
  * (default off: measured on B200, cfg3, 1.294 ms with against 1.245 ms without -- the WHILE body gains

@@ -341,13 +341,15 @@ def test_damping_ladder_is_invisible(golden):
         s1, P1, i1, t1 = prob.lm_run(g["P0"], 100)
         n1 = prob.last_run_stats()[1]
         for cap in (2, 4):
-            for mode in (1, 2):
-                prob.set_ladder(cap)
-                prob.set_loop_mode(mode)
-                s2, P2, i2, t2 = prob.lm_run(g["P0"], 100)
-                assert i1 == i2 and s1 == s2, (case, cap, mode, i1, i2)
-                assert np.array_equal(t1, t2) and np.array_equal(P1, P2), (case, cap, mode)
-            assert prob.last_run_stats()[1] <= n1
+            for start in (1, 2, 0):
+                for mode in (1, 2):
+                    prob.set_ladder(cap)
+                    prob.set_ladder_start(start)
+                    prob.set_loop_mode(mode)
+                    s2, P2, i2, t2 = prob.lm_run(g["P0"], 100)
+                    assert i1 == i2 and s1 == s2, (case, cap, start, mode, i1, i2)
+                    assert np.array_equal(t1, t2) and np.array_equal(P1, P2), (case, cap, start, mode)
+                assert prob.last_run_stats()[1] <= n1
         rejected = np.where(t1[:, 3] == 0)[0]
         cuts = {3, i1 - 1} | ({int(rejected[0]) + 2, int(rejected[0]) + 3} if len(rejected) else set())
         for cut in sorted(c for c in cuts if 0 < c < i1):

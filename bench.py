@@ -223,6 +223,69 @@ def workload_config(name, scale, c, offs, gpus):
                   "L2-resident across LM iterations, as in production use"}
 
 
+def reference_python_seconds():
+    """What the UNMODIFIED Python/sympy reference itself took on its own CPU-runnable cases: measured while
+    the golden fixtures were generated (oracle/make_golden.py, build container, one core as the reference
+    runs) and committed inside tests/golden/*.npz as ref_seconds = [initial guess, first Jacobian,
+    refinement loop, Jacobian share of the loop].  The reference cannot travel to the GPU box, so these are
+    quoted, not re-measured; BASELINE.md's 0.2-5 iterations/s sits beside them."""
+    out = {}
+    for case in ("cfg1", "cfg1n", "cfg2", "itest"):
+        f = os.path.join(ROOT, "tests", "golden", case + ".npz")
+        if not os.path.exists(f):
+            continue
+        z = np.load(f)
+        if "ref_seconds" not in z.files:
+            continue
+        loop_s, its = float(z["ref_seconds"][2]), int(z["iters"])
+        out[case] = {"loop_s": round(loop_s, 3), "iterations": its, "iterations_per_s": round(its / loop_s, 3),
+                     "points": int(z["view_offsets"][-1]), "views": int(len(z["view_offsets"]) - 1)}
+    return {"source": "tests/golden/*.npz ref_seconds (src/calibrate.py:117-171 run unmodified by "
+                      "oracle/make_golden.py in the build container; not re-measured here)", "cases": out}
+
+
+def time_reference_python(case="cfg1", timeout=240):
+    """Runs the UNMODIFIED Python reference (vendored, git-ignored copy under baseline/_ref, see
+    oracle/vendor_reference.py) on one of its own CPU-runnable cases in a subprocess on this box's host
+    cores and returns its JSON (oracle/time_reference.py), or None when the copy or sympy is absent."""
+    ref_root = os.path.join(ROOT, "baseline", "_ref")
+    if not os.path.isdir(os.path.join(ref_root, "src")):
+        return None
+    env = dict(os.environ, CALIB_REF_ROOT=ref_root, CUDA_VISIBLE_DEVICES="")
+    try:
+        res = subprocess.run([sys.executable, os.path.join(ROOT, "oracle", "time_reference.py"), case],
+                             capture_output=True, text=True, timeout=timeout, env=env)
+        if res.returncode != 0:
+            return {"case": case, "error": (res.stderr or "").strip().splitlines()[-1:]}
+        return json.loads(res.stdout.strip().splitlines()[-1])
+    except Exception as e:      # a missing sympy, a time-out: the quoted figures remain
+        return {"case": case, "error": repr(e)}
+
+
+def reference_python_block(product=None, case="cfg1"):
+    """cpu_baseline.reference_python: the real reference timed HERE on `case` (kind "reference"), with the
+    product's own run of the same case beside it when `product` (a callable returning sse, P, iterations,
+    ms) is given."""
+    r = time_reference_python(case)
+    if r is None:
+        return {"unavailable": "baseline/_ref not present (oracle/vendor_reference.py was not run where "
+                               "/root/reference exists)", "quoted": reference_python_seconds()}
+    if "error" in r:
+        return {"unavailable": r["error"], "quoted": reference_python_seconds()}
+    P_ref = np.asarray(r.pop("P"))
+    out = {"kind": "reference", "cores": 1, "what": "Calibrator.refineCalibrationParameters of the unmodified "
+           "Python/sympy reference (baseline/_ref), its own case " + case + ", this box's host cores", **r}
+    if product is not None:
+        sse, P, iters, ms = product()
+        out["product_same_case"] = {
+            "ms_per_refinement": ms, "iterations": int(iters), "sse": float(sse),
+            "iterations_equal": bool(int(iters) == int(r["iterations"])),
+            "max_abs_param_diff": float(np.max(np.abs(np.asarray(P) - P_ref))),
+            "sse_abs_diff": abs(float(sse) - float(r["sse"])),
+            "speedup_by_time": 1e3 * r["refine_call_s"] / ms if ms else None}
+    return out
+
+
 # ---- reference arm: the CPU restatement, no product import --------------------------------------------
 def run_reference_arm(args):
     if int(os.environ.get("RANK", "0")) != 0:
@@ -250,7 +313,9 @@ def run_reference_arm(args):
         "cpu_baseline": {"value": val, "unit": "LM iterations/s", "cores": host_threads(), "kind": "port",
                          "sample": "each step = one complete LM run of the workload; C restatement of the "
                                    "reference's path (oracle/calib_oracle.c, OpenMP over all host threads); the "
-                                   "Python/sympy reference cannot travel to this box nor hold this workload's dense J"},
+                                   "Python/sympy reference cannot travel to this box nor hold this workload's dense J",
+                         "reference_python_s": reference_python_seconds(),
+                         "reference_python": None if args.no_python_reference else reference_python_block()},
         "e2e": {"value": val, "unit": "LM iterations/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
         "product_imported": bool("camera_calibration_b200" in sys.modules),
@@ -466,7 +531,6 @@ def bench_calibration(args, env, name, scale, steps, warmup, light=False):
     if args.loop_mode:
         prob.set_loop_mode(args.loop_mode)
     prob.set_ladder(args.ladder)
-    prob.set_pdl(args.pdl)
     transport = "none"
     if world > 1:
         from camera_calibration_b200 import sharding
@@ -507,7 +571,6 @@ def bench_calibration(args, env, name, scale, steps, warmup, light=False):
         def e2e_step():
             p2 = cc.Problem(model, offs, mp_pin, sp_pin, device=local)     # borrows prob's communicator (set_default)
             p2.set_ladder(args.ladder)
-            p2.set_pdl(args.pdl)
             if args.loop_mode:
                 p2.set_loop_mode(args.loop_mode)
             _, _, it, _ = p2.lm_run(Ploc, MAX_ITERS, want_trace=False)
@@ -649,7 +712,8 @@ def bench_calibration(args, env, name, scale, steps, warmup, light=False):
                        ms_per_refinement=1e3 * dt_o,
                        sample=f"one complete LM run of the workload: {it_o} iterations, {ev_o} Jacobian passes, "
                               f"{dt_o:.2f} s; C restatement of the reference's path (oracle/calib_oracle.c, OpenMP)",
-                       jacobian_rows_per_s=2.0 * offs_a[-1] * ev_o / dt_o)
+                       jacobian_rows_per_s=2.0 * offs_a[-1] * ev_o / dt_o,
+                       reference_python_s=reference_python_seconds())
             parity_key = "parity_vs_oracle"
             parity = parity_block(P_run, sse, iters, tr_run, P_o, sse_o, it_o, tr_o, "oracle/calib_oracle.c (CPU)")
     else:
@@ -711,11 +775,12 @@ def main():
     ap.add_argument("--loop-mode", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-secondary", action="store_true")
+    ap.add_argument("--no-python-reference", action="store_true",
+                    help="skip timing the vendored Python reference on cfg1 (about 25 s of host time)")
     ap.add_argument("--problems", type=int, default=8192)
     ap.add_argument("--cpu-sample", type=int, default=512)
     ap.add_argument("--ladder", type=int, default=4, choices=[1, 2, 4],
                     help="damping ladder: trial steps taken ahead of the accept/reject decisions (1 = off)")
-    ap.add_argument("--pdl", type=int, default=0, choices=[0, 1], help="programmatic dependent launch inside the graphs")
     ap.add_argument("--transport", default="auto", choices=["auto", "peer", "nccl"],
                     help="sharded views: in-kernel all-reduce over NVLink peer memory, or NCCL all-reduces")
     args = ap.parse_args()
@@ -774,11 +839,26 @@ def main():
                                                       "e2e", "config")}
             if rank == 0:
                 line["secondary"] = sec
+        if (rank == 0 and world == 1 and not args.no_cpu_baseline and not args.no_python_reference
+                and isinstance(line.get("cpu_baseline"), dict)):
+            line["cpu_baseline"]["reference_python"] = reference_python_block(lambda: product_on_golden("cfg1", local))
         if rank == 0:
             print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def product_on_golden(case, device):
+    """the product on one of the reference's own cases (tests/golden/<case>.npz): sse, P, iterations, device ms"""
+    import camera_calibration_b200 as cc
+    z = np.load(os.path.join(ROOT, "tests", "golden", case + ".npz"))
+    prob = cc.Problem(int(z["model"]), z["view_offsets"], z["model_pts"], z["sensor_pts"], device=device)
+    for _ in range(3):
+        sse, P, iters, _ = prob.lm_run(z["P0"].copy(), int(z["maxIters"]))
+    ms = prob.last_run_stats()[0]
+    prob.close()
+    return sse, P, iters, ms
 
 
 def run_calibration_with_parity(args, env, name, scale, steps, warmup, light):

@@ -90,7 +90,6 @@ def lib():
         "calib_set_cost_staging": (c_int, [_vp, c_int]),
         "calib_set_ladder": (c_int, [_vp, c_int]),
         "calib_set_ladder_start": (c_int, [_vp, c_int]),
-        "calib_set_pdl": (c_int, [_vp, c_int]),
         "calib_host_alloc": (_vp, [ctypes.c_size_t]),
         "calib_host_free": (None, [_vp]),
         "calib_host_gather": (c_int, [_vp, _vp, _i64, c_i64, c_int]),

@@ -249,9 +249,6 @@ class Problem:
         """candidates of the pass that follows an accepted step (1, 2, or 0 = adaptive, the default)"""
         self._check(self._L.calib_set_ladder_start(self._h, int(candidates)))
 
-    def set_pdl(self, on):
-        self._check(self._L.calib_set_pdl(self._h, 1 if on else 0))
-
     def set_loop_mode(self, mode):
         """0 auto, 1 host-driven iteration graphs, 2 device-driven WHILE graph."""
         self._check(self._L.calib_set_loop_mode(self._h, int(mode)))

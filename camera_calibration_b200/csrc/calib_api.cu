@@ -96,8 +96,6 @@ struct calib_handle {
     bool comm_owned = false;
     int nranks = 1, rank = 0;
     std::shared_ptr<PeerComm> peer;        // in-kernel exchange over NVLink peer memory
-    int pdl = 0;                           // programmatic dependent launch between the kernels of the iteration (measured: no gain, off)
-    bool pdl_now = false;                  // set while the iteration is being captured into a graph
     int ladder = kJMax;                    // cap of the damping ladder (1 = one candidate per pass)
     int ladder_start = 0;                  // candidates of the pass that follows an accepted step: 1, 2, 0 = adaptive
     int transport = 0;                     // 0 auto (peer memory when attached, else NCCL), 1 NCCL, 2 peer memory
@@ -248,10 +246,10 @@ static void ctx_release(calib_handle* h) {
 // (profiles/r2q_graph_patch.txt: 4 us against 540 us).  At most kLoopCacheMax graphs wait per process; the
 // oldest beyond that are destroyed when the next handle is created (under its upload).
 struct LoopKey {
-    int device, model, ev_blocks, co_blocks, sc_groups, bs_groups, tma, pdl;
+    int device, model, ev_blocks, co_blocks, sc_groups, bs_groups, tma;
     bool operator==(const LoopKey& o) const {
         return device == o.device && model == o.model && ev_blocks == o.ev_blocks && co_blocks == o.co_blocks &&
-               sc_groups == o.sc_groups && bs_groups == o.bs_groups && tma == o.tma && pdl == o.pdl;
+               sc_groups == o.sc_groups && bs_groups == o.bs_groups && tma == o.tma;
     }
 };
 struct CachedLoop {
@@ -575,9 +573,8 @@ static cudaError_t device_func_attributes(int device) {
     set(k_cost<1, false, true>, kCostDynSmem); set(k_cost<1, true, true>, kCostDynSmem);
     set(k_eval<0>, kEvalDynSmem); set(k_eval<1>, kEvalDynSmem);
 #ifdef CALIB_EXPERIMENT_PERSISTENT
-    set(k_lm_persistent<0, true, 1>, kPersistDynSmem); set(k_lm_persistent<1, true, 1>, kPersistDynSmem);
-    set(k_lm_persistent<0, false, 1>, kPersistDynSmem); set(k_lm_persistent<1, false, 1>, kPersistDynSmem);
-    set(k_lm_persistent<0, false, 2>, kPersistDynSmem); set(k_lm_persistent<1, false, 2>, kPersistDynSmem);
+    set(k_lm_persistent<0, true>, kPersistDynSmem); set(k_lm_persistent<1, true>, kPersistDynSmem);
+    set(k_lm_persistent<0, false>, kPersistDynSmem); set(k_lm_persistent<1, false>, kPersistDynSmem);
 #endif
     if (e == cudaSuccess && device >= 0 && device < 64) done[device] = true;
     return e;
@@ -769,13 +766,6 @@ extern "C" int calib_set_loop_mode(calib_t* h, int mode) {
     return CALIB_OK;
 }
 
-extern "C" int calib_set_pdl(calib_t* h, int on) {
-    if (!h) return fail(nullptr, CALIB_E_ARG, "NULL handle");
-    if (h->pdl != (on ? 1 : 0)) drop_graph(h);
-    h->pdl = on ? 1 : 0;
-    return CALIB_OK;
-}
-
 extern "C" int calib_set_ladder(calib_t* h, int max_candidates) {
     if (!h) return fail(nullptr, CALIB_E_ARG, "NULL handle");
     if (max_candidates != 1 && max_candidates != 2 && max_candidates != kJMax)
@@ -847,23 +837,13 @@ namespace {
 
 enum { KEVAL = 0, KSCHUR = 1, KBACK = 2, KCOST = 3, KSOLVE = 4 };
 
-// Kernel launch of the iteration.  With h->pdl_now the launch carries the programmatic-dependent-launch
-// attribute: under stream capture the edge to the previous kernel node becomes a programmatic one, the
-// blocks of this kernel are scheduled while the previous kernel drains (every kernel of the iteration
-// triggers its dependents at its top and waits with griddepcontrol.wait before it reads anything the
-// previous kernel wrote), and the ~3 us between two dependent kernel nodes shrinks.
+// Kernel launch of the iteration on the handle's stream.
 template <typename... KArgs, typename... Args>
 cudaError_t launch_iter(calib_handle* h, void (*kern)(KArgs...), int grid, int block, size_t smem, Args... args) {
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof cfg);
     cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3((unsigned)block);
     cfg.dynamicSmemBytes = smem; cfg.stream = h->stream;
-    cudaLaunchAttribute at[1];
-    if (h->pdl_now) {
-        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        at[0].val.programmaticStreamSerializationAllowed = 1;
-        cfg.attrs = at; cfg.numAttrs = 1;
-    }
     return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
 }
 
@@ -1008,9 +988,7 @@ int build_graph(calib_handle* h) {
     h->dev.use_cond = 0;
     CUDA_TRY(h, cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
     Launcher ln{h, false};
-    h->pdl_now = h->pdl != 0 && !nccl_active(h);
     int rc = enqueue_iteration_any(h, ln);
-    h->pdl_now = false;
     cudaError_t e = cudaStreamEndCapture(h->stream, &g);
     if (rc) { if (g) cudaGraphDestroy(g); return rc; }
     CUDA_TRY(h, e);
@@ -1028,7 +1006,7 @@ int build_loop_graph(calib_handle* h) {
     ScopeTimer tm_("build_loop_graph");
     const Dev& d0 = h->dev;
     const LoopKey key{h->device, h->model, d0.ev_blocks, d0.co_blocks, d0.sc_groups, d0.bs_groups,
-                      cost_uses_tma(h) ? 1 : 0, (h->pdl != 0 && !nccl_active(h)) ? 1 : 0};
+                      cost_uses_tma(h) ? 1 : 0};
     const bool cacheable = !nccl_active(h);
     if (cacheable) {
         CachedLoop* c = nullptr;
@@ -1078,9 +1056,7 @@ int build_loop_graph(calib_handle* h) {
     e = cudaStreamBeginCaptureToGraph(h->stream, body, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal);
     if (e != cudaSuccess) { h->dev.use_cond = 0; cudaGraphDestroy(g); CUDA_TRY(h, e); }
     Launcher ln{h, false};
-    h->pdl_now = h->pdl != 0 && !nccl_active(h);
     int rc = enqueue_iteration_any(h, ln);
-    h->pdl_now = false;
     cudaGraph_t got = nullptr;
     e = cudaStreamEndCapture(h->stream, &got);
     h->dev.use_cond = 0;
@@ -1174,37 +1150,7 @@ bool cost_uses_tma(const calib_handle* h) {
 }
 
 #ifdef CALIB_EXPERIMENT_PERSISTENT
-
-template <int MODEL, bool TMA, int PF>
-int launch_persistent_t(calib_handle* h) {
-    auto kern = k_lm_persistent<MODEL, TMA, PF>;
-    const size_t smem = kPersistDynSmem;     // the evaluation pass's hand-off rings / the cost pass's bulk-copy rings
-    if (h->persist_blocks <= 0) {
-        int per_sm = 0;
-        CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kBlockThreads, smem));
-        if (per_sm < 1) return fail(h, CALIB_E_CUDA, "persistent kernel: no block fits an SM");
-        h->persist_blocks = h->n_sm;      // one block per SM: the evaluation sweep is sized for that
-    }
-    const Dev& d = h->dev;
-    // as many blocks as the widest phase can use, at most one per SM (all must be co-resident)
-    int want = std::max(std::max(d.ev_blocks, d.co_blocks), d.sc_groups * (int)kJMax);
-    want = std::max(1, std::min(want, h->persist_blocks));
-    void* args[] = {(void*)&h->dev};
-    CUDA_TRY(h, cudaLaunchCooperativeKernel((const void*)kern, dim3((unsigned)want), dim3(kBlockThreads), args, smem, h->stream));
-    return CALIB_OK;
-}
-
-int launch_persistent(calib_handle* h) {
-    static const int pf = [] { const char* e = getenv("CALIB_PERSIST_PF"); return e ? atoi(e) : 1; }();
-    const bool tma = cost_uses_tma(h);
-    h->dev.use_cond = 0;
-    if (h->model == 0) {
-        if (tma) return launch_persistent_t<0, true, 1>(h);
-        return pf == 2 ? launch_persistent_t<0, false, 2>(h) : launch_persistent_t<0, false, 1>(h);
-    }
-    if (tma) return launch_persistent_t<1, true, 1>(h);
-    return pf == 2 ? launch_persistent_t<1, false, 2>(h) : launch_persistent_t<1, false, 1>(h);
-}
+#include "experiments/calib_persistent_host.inc"
 #else
 int launch_persistent(calib_handle* h) { return fail(h, CALIB_E_STATE, "loop mode 3 is not in this build"); }
 #endif
@@ -1259,12 +1205,6 @@ int lm_start(calib_handle* h, int maxIters, double lam0, double lam_min, double 
     const bool device_loop = !prof && mode == 2;
     if (!prof && !persistent) {
         int rc = device_loop ? build_loop_graph(h) : build_graph(h);
-        if (rc && h->pdl) {          // a driver that rejects programmatic edges here: plain edges
-            h->pdl = 0;
-            cudaGetLastError();
-            drop_graph(h);
-            rc = device_loop ? build_loop_graph(h) : build_graph(h);
-        }
         RC(rc);
     }
     for (auto& pe : h->prof_events) { cudaEventDestroy(pe.second.first); cudaEventDestroy(pe.second.second); }

@@ -133,10 +133,6 @@ constexpr size_t kStampWords = (size_t)4 * kStampBlocks * 8 + (size_t)2 * kPStam
 #define PSTAMP(d, pass, slot) do {} while (0)
 #endif
 
-// Programmatic dependent launch (see launch_iter in calib_api.cu): no-ops without the launch attribute.
-__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
-__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
-
 // threadIdx.x through a volatile asm: the phase functions of the iteration take their thread indices
 // this way so that, inlined one after the other into the persistent kernel, nothing derived from them
 // is kept alive (hoisted, common-subexpression'd) from one phase across the sweeps of another -- the
@@ -264,10 +260,9 @@ __device__ __forceinline__ void accum_BD_ring(const double2* slot, double (&acc)
 // boundaries, so a load is never waited for inside the FP64 stream.  `begin(piece, index)` runs
 // after the view constants are in sview (warp-synchronised), `body(point)` per point of the
 // lane, `end(piece, index)` with all 32 lanes converged.
-// PF: how many 32-point steps ahead the points are fetched inside a piece (1 or 2).  A sweep that is
-// bound by FP64 issue needs 1; the cost sweep has so little arithmetic per point that one step in
-// flight per warp leaves it waiting for L2 (16 warps x 1.3 KB per SM against ~1300 cycles).
-template <int NV, int PF, bool COUNTED = false, class Begin, class Body, class End>
+// (Measured and rejected, profiles/README.md: two steps of look-ahead, a counted loop, and a two-stage
+// software-pipelined body.)
+template <int NV, class Begin, class Body, class End>
 __device__ __forceinline__ void sweep_pieces(const Dev& d, const Piece* __restrict__ pieces, const WarpRec& rec,
                                              const ViewC* const (&views)[NV], ViewC (&sview)[NV], int lane,
                                              Begin begin, Body body, End end) {
@@ -298,99 +293,11 @@ __device__ __forceinline__ void sweep_pieces(const Dev& d, const Piece* __restri
         }
         begin(cur, pi);
         if (lane >= cur.count && has_next && lane < nxt.count) load_point(d, (long long)nxt.start + lane, pn);
-        if constexpr (PF == 1) {
-            if constexpr (COUNTED) {
-            // the same loop with a step count and a running index: the piece's start and count are not
-            // live inside it (register pressure: see profiles/README.md, static look at k_eval)
-            const int steps = cur.count > lane ? (cur.count - lane + 31) >> 5 : 0;
-            long long idx = (long long)cur.start + lane;
-            for (int sidx = 0; sidx < steps; ++sidx) {
-                const Pt p = pn;
-                idx += 32;
-                if (sidx + 1 < steps) load_point(d, idx, pn);
-                else if (has_next && lane < nxt.count) load_point(d, (long long)nxt.start + lane, pn);
-                body(p);
-            }
-            } else {
-            for (int i = lane; i < cur.count; i += 32) {
-                const Pt p = pn;
-                if (i + 32 < cur.count) load_point(d, (long long)cur.start + i + 32, pn);
-                else if (has_next && lane < nxt.count) load_point(d, (long long)nxt.start + lane, pn);
-                body(p);
-            }
-            }
-        } else {
-            Pt pn2 = pn;
-            if (lane + 32 < cur.count) load_point(d, (long long)cur.start + lane + 32, pn2);
-            for (int i = lane; i < cur.count; i += 32) {
-                const Pt p = pn;
-                pn = pn2;
-                if (i + 64 < cur.count) load_point(d, (long long)cur.start + i + 64, pn2);
-                else if (i + 32 >= cur.count && has_next && lane < nxt.count) load_point(d, (long long)nxt.start + lane, pn);
-                body(p);
-            }
-        }
-        __syncwarp();
-        end(cur, pi);
-        cur = nxt;
-    }
-}
-
-// The same sweep with the per-point work split in two stages, software-pipelined inside a piece:
-// stage1 (the dependent chain: projection, distortion, residual) of point i+1 is issued together with
-// stage2 (the independent accumulations) of point i.  With two warps per scheduler the chain of the
-// second evaluation sweep is otherwise not covered (58 % FP64 issue); the accumulation order per lane is
-// unchanged, so the sums are bit-identical to sweep_pieces.  EXPERIMENT (-DCALIB_EVAL_STAGED=1), not the
-// default: at 255 registers ptxas does not interleave the stages and the copies cost 4 % (cfg3 k_eval
-// 63.8 against 61.2 us, profiles/r1z_staged.txt).
-template <int NV, class Begin, class Stage1, class Stage2, class End>
-__device__ __forceinline__ void sweep_pieces_staged(const Dev& d, const Piece* __restrict__ pieces, const WarpRec& rec,
-                                                    const ViewC* const (&views)[NV], ViewC (&sview)[NV], int lane,
-                                                    Begin begin, Stage1 stage1, Stage2 stage2, End end) {
-    const int p0 = rec.p0, p1 = rec.p1;
-    if (p0 >= p1) return;
-    Piece cur = rec.first;
-    Pt pn;
-    if (lane < cur.count) load_point(d, (long long)cur.start + lane, pn);
-    double vn[NV];
-#pragma unroll
-    for (int j = 0; j < NV; ++j) {
-        vn[j] = 0.0;
-        if (lane < kViewDoubles) vn[j] = reinterpret_cast<const double*>(views[j] + cur.view)[lane];
-    }
-    for (int pi = p0; pi < p1; ++pi) {
-        const bool has_next = pi + 1 < p1;
-        Piece nxt = cur;
-        if (has_next) nxt = pieces[pi + 1];
-        __syncwarp();
-        if (lane < kViewDoubles) {
-#pragma unroll
-            for (int j = 0; j < NV; ++j) reinterpret_cast<double*>(&sview[j])[lane] = vn[j];
-        }
-        __syncwarp();
-        if (has_next && lane < kViewDoubles) {
-#pragma unroll
-            for (int j = 0; j < NV; ++j) vn[j] = reinterpret_cast<const double*>(views[j] + nxt.view)[lane];
-        }
-        begin(cur, pi);
-        if (lane >= cur.count && has_next && lane < nxt.count) load_point(d, (long long)nxt.start + lane, pn);
-        int i = lane;
-        if (i < cur.count) {
-            auto fetch = [&](int at) {
-                if (at + 32 < cur.count) load_point(d, (long long)cur.start + at + 32, pn);
-                else if (has_next && lane < nxt.count) load_point(d, (long long)nxt.start + lane, pn);
-            };
-            Pt p = pn;
-            fetch(i);
-            auto prev = stage1(p);
-            for (i += 32; i < cur.count; i += 32) {
-                p = pn;
-                fetch(i);
-                const auto o = stage1(p);
-                stage2(prev);
-                prev = o;
-            }
-            stage2(prev);
+        for (int i = lane; i < cur.count; i += 32) {
+            const Pt p = pn;
+            if (i + 32 < cur.count) load_point(d, (long long)cur.start + i + 32, pn);
+            else if (has_next && lane < nxt.count) load_point(d, (long long)nxt.start + lane, pn);
+            body(p);
         }
         __syncwarp();
         end(cur, pi);

@@ -17,7 +17,7 @@ constexpr size_t kCostDynSmem = kBlockWarps * sizeof(CostRing);
 
 extern __shared__ __align__(128) unsigned char dyn_smem[];
 
-template <bool TMA, int D, int WS, int NV, int PF, class Begin, class Body, class End>
+template <bool TMA, int D, int WS, int NV, class Begin, class Body, class End>
 __device__ __forceinline__ void sweep(const Dev& d, const Piece* __restrict__ pieces, const WarpRec& rec,
                                       const ViewC* const (&views)[NV], ViewC (&sview)[NV], int warp,
                                       unsigned long long* bars, int lane, Begin begin, Body body, End end) {
@@ -25,7 +25,7 @@ __device__ __forceinline__ void sweep(const Dev& d, const Piece* __restrict__ pi
         PointRing<D, WS>* ring = reinterpret_cast<PointRing<D, WS>*>(dyn_smem);
         sweep_windows<D, WS, NV>(d, pieces, rec, views, sview, ring[warp], bars, lane, begin, body, end);
     } else {
-        sweep_pieces<NV, PF>(d, pieces, rec, views, sview, lane, begin, body, end);
+        sweep_pieces<NV>(d, pieces, rec, views, sview, lane, begin, body, end);
     }
 }
 
@@ -242,9 +242,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
     const int w = blockIdx.x * kEvalPairs + pair;
     WarpRec rec;                       // issued together with the state load below: one round trip
     rec.p0 = rec.p1 = 0;
-    pdl_trigger();
-    if (w < d.ev_warps) rec = d.ev_rec[w];        // static: may be read before the previous kernel is done
-    pdl_wait();
+    if (w < d.ev_warps) rec = d.ev_rec[w];
     const LmState* st = d.st;
     if (st->done || !st->need_eval) return;
     __shared__ EvalSmem sm;
@@ -315,7 +313,6 @@ __device__ __forceinline__ void lm_accept(const Dev& d) {
 
 template <bool COND>
 __global__ void k_accept(Dev d) {
-    pdl_wait();
     if (d.st->done) return;
     lm_accept<COND>(d);
 }
@@ -330,7 +327,7 @@ struct __align__(16) CostSmem {
     int s_last;
 };
 
-template <int MODEL, bool TMA, int NJ, int PF>
+template <int MODEL, bool TMA, int NJ>
 __device__ __forceinline__ void cost_sweep(const Dev& d, const WarpRec& rec, int cur, double (*sc)[16],
                                            ViewC (&sview)[kJMax], unsigned long long* bars, int warp, int lane,
                                            double (&e)[kJMax]) {
@@ -339,7 +336,7 @@ __device__ __forceinline__ void cost_sweep(const Dev& d, const WarpRec& rec, int
     for (int j = 0; j < NJ; ++j) views[j] = d.views + (long long)trial_buf(cur, j) * d.M;
     const ViewC* const (&cviews)[NJ] = views;
     ViewC (&sv)[NJ] = reinterpret_cast<ViewC (&)[NJ]>(sview);
-    sweep<TMA, kCostStages, kWinSteps, NJ, PF>(d, d.co_piece, rec, cviews, sv, warp, bars, lane,
+    sweep<TMA, kCostStages, kWinSteps, NJ>(d, d.co_piece, rec, cviews, sv, warp, bars, lane,
         [&](const Piece&, int) {},
         [&](const Pt& p) {
 #pragma unroll
@@ -355,7 +352,7 @@ __device__ __forceinline__ void cost_sweep(const Dev& d, const WarpRec& rec, int
 // Block *vbp of the cost pass (vbp as in eval_block): the J trial costs of its warps' chunks -> row vb
 // of partC.  Called by all threads of a block; starts with a barrier-protected load of the trial
 // shared parameters.
-template <int MODEL, bool TMA, int PF>
+template <int MODEL, bool TMA>
 __device__ __forceinline__ void cost_block(const Dev& d, CostSmem& sm, const volatile int* vbp, int cur, int J, const WarpRec& rec) {
     constexpr int L = ModelTraits<MODEL>::L;
     const int tid = tid_now();
@@ -369,9 +366,9 @@ __device__ __forceinline__ void cost_block(const Dev& d, CostSmem& sm, const vol
     double e[kJMax];
 #pragma unroll
     for (int j = 0; j < kJMax; ++j) e[j] = 0.0;
-    if (J == 1) cost_sweep<MODEL, TMA, 1, PF>(d, rec, cur, sm.sc, sm.sview[warp], sm.bars[warp], warp, lane, e);
-    else if (J == 2) cost_sweep<MODEL, TMA, 2, PF>(d, rec, cur, sm.sc, sm.sview[warp], sm.bars[warp], warp, lane, e);
-    else cost_sweep<MODEL, TMA, kJMax, PF>(d, rec, cur, sm.sc, sm.sview[warp], sm.bars[warp], warp, lane, e);
+    if (J == 1) cost_sweep<MODEL, TMA, 1>(d, rec, cur, sm.sc, sm.sview[warp], sm.bars[warp], warp, lane, e);
+    else if (J == 2) cost_sweep<MODEL, TMA, 2>(d, rec, cur, sm.sc, sm.sview[warp], sm.bars[warp], warp, lane, e);
+    else cost_sweep<MODEL, TMA, kJMax>(d, rec, cur, sm.sc, sm.sview[warp], sm.bars[warp], warp, lane, e);
     STAMP(d, 3, 1);
 #pragma unroll
     for (int j = 0; j < kJMax; ++j) {
@@ -407,9 +404,7 @@ __global__ void __launch_bounds__(kBlockThreads, 2) k_cost(Dev d, int fuse_accep
     const int w = blockIdx.x * kBlockWarps + warp;
     WarpRec rec;
     rec.p0 = rec.p1 = 0;
-    pdl_trigger();
     if (w < d.co_warps) rec = d.co_rec[w];
-    pdl_wait();
     LmState* st = d.st;
     if (st->done) {   // also after a failed exchange: the WHILE node must not spin
         if (COND) { if (blockIdx.x == 0 && threadIdx.x == 0) cudaGraphSetConditional(d.cond, 0u); }
@@ -419,7 +414,7 @@ __global__ void __launch_bounds__(kBlockThreads, 2) k_cost(Dev d, int fuse_accep
     __shared__ int s_vb;
     if (threadIdx.x == 0) s_vb = blockIdx.x;
     const int J = st->J;
-    cost_block<MODEL, TMA, 1>(d, sm, &s_vb, st->cur, J, rec);
+    cost_block<MODEL, TMA>(d, sm, &s_vb, st->cur, J, rec);
     if (threadIdx.x < kJMax) __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) {

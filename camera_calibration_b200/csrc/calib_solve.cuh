@@ -337,8 +337,6 @@ __device__ __forceinline__ bool schur_tail(const Dev& d, SchurSmem<MODEL>& sm, c
 // ticket) runs the tail.
 template <int MODEL>
 __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) {
-    pdl_trigger();
-    pdl_wait();
     LmState* st = d.st;
     if (st->done) return;
     __shared__ SchurSmem<MODEL> sm;
@@ -371,7 +369,6 @@ __global__ void __launch_bounds__(kBlockThreads) k_schur(Dev d, int fuse_solve) 
 template <int MODEL>
 __global__ void k_solve(Dev d) {
     constexpr int L = ModelTraits<MODEL>::L;
-    pdl_wait();
     if (d.st->done) return;
     __shared__ double sdense[kJMax * (L * L + L)];
     const PassCtx c = pass_ctx(*d.st);
@@ -457,8 +454,6 @@ __device__ __forceinline__ void backsub_load_dc(const Dev& d, BacksubSmem& sm, i
 
 template <int MODEL>
 __global__ void __launch_bounds__(kBlockThreads) k_backsub(Dev d) {
-    pdl_trigger();
-    pdl_wait();
     LmState* st = d.st;
     if (st->done) return;
     __shared__ BacksubSmem sm;

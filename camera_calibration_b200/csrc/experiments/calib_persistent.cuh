@@ -149,8 +149,8 @@ __device__ __noinline__ void accept_published_phase(const Dev& d, LmState& st) {
 }
 
 // TMA: the cost sweep streams the detections through the bulk-copy ring (dynamic shared memory:
-// kCostDynSmem); PF: register prefetch depth of the cost sweep otherwise.
-template <int MODEL, bool TMA, int PF>
+// kCostDynSmem).
+template <int MODEL, bool TMA>
 __global__ void __launch_bounds__(kBlockThreads, 1) k_lm_persistent(const __grid_constant__ Dev d) {
     // Nothing of the loop is kept in registers across a phase: the state copy, the barrier target and
     // the virtual-block counters live in shared memory and the grid geometry is re-read from the
@@ -218,7 +218,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) k_lm_persistent(const __grid
             WarpRec rec;
             rec.p0 = rec.p1 = 0;
             if (w < d.co_warps) rec = d.co_rec[w];
-            cost_block<MODEL, TMA, PF>(d, sm.c, &s_vb, s_st.cur, s_st.J, rec);
+            cost_block<MODEL, TMA>(d, sm.c, &s_vb, s_st.cur, s_st.J, rec);
             __syncthreads();
             if (tid_now() == 0) s_vb += gridDim.x;
             __syncthreads();

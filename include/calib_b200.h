@@ -91,11 +91,6 @@ int calib_set_ladder(calib_t* h, int max_candidates);
  * keeps happening, else 1.  Bit-identical results. */
 int calib_set_ladder_start(calib_t* h, int candidates);
 
-/* Programmatic dependent launch between the kernels of the iteration inside the captured graphs
- * (default off: measured on B200, cfg3, 1.294 ms with against 1.245 ms without -- the WHILE body gains
- * nothing from programmatic edges; results are identical either way). */
-int calib_set_pdl(calib_t* h, int on);
-
 /* How the trial-cost sweep brings the detections in: 1 = bulk copies (TMA) into a per-warp
  * shared-memory ring, 0 = coalesced loads with register prefetch, -1 (default) = by size (the ring
  * when the detections exceed what L2 keeps between sweeps).  Same points, same code; a lane's share of a

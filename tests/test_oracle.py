@@ -198,16 +198,13 @@ def test_device_atan_polynomial():
                             "calib_device.cuh")).read()
     body = src[src.index("double atan_pos("):]
     body = body[:body.index("return big")]
-    pairs = re.findall(r"a(\d) = fma\(ATAN_C\((\d+), ([-0-9.e]+)\), q, ATAN_C\((\d+), ([-0-9.e]+)\)\)", body)
+    pairs = re.findall(r"a(\d) = fma\(([-0-9.e]+), q, ([-0-9.e]+)\)", body)
     assert [int(p[0]) for p in pairs] == list(range(10))
     c = []
-    for n, ihi, hi, ilo, lo in pairs:
-        assert int(ilo) == 2 * int(n) and int(ihi) == 2 * int(n) + 1
+    for n, hi, lo in pairs:
         c += [float(lo), float(hi)]
-    # the constant-memory table the kernels really read holds the same numbers, in that order
-    table = src[src.index("kAtanC[22] = {") + len("kAtanC[22] = {"):]
-    table = [float(x) for x in table[:table.index("}")].replace("\n", " ").split(",")]
-    assert table[:20] == c and table[20:] == [1.5707963267948966, 6.123233995736766e-17]
+    tail = src[src.index("return big", src.index("double atan_pos(")):]
+    assert "1.5707963267948966" in tail[:120] and "6.123233995736766e-17" in tail[:120]
 
     def atan_small(z):
         q = z * z

@@ -650,8 +650,7 @@ def bench_calibration(args, env, name, scale, steps, warmup, light=False):
                                  "api": "Calibrator.refineCalibrationParameters(A, W, k, allDetections, maxIters): "
                                         "list of per-view arrays in, (sse, A, W, k) out"}
 
-    # ---- per-kernel times of the per-launch pipeline (same device code as the persistent kernel's
-    # phases): CUDA events around back-to-back launches on the library's stream, L2-warm as between the
+    # ---- per-kernel times of the pass (the kernels inside the WHILE graph's body, launched one by one): CUDA events around back-to-back launches on the library's stream, L2-warm as between the
     # iterations of a run, and after an L2 flush before every launch
     kt = {}
     for i, nm in enumerate(["k_eval", "k_schur", "k_backsub", "k_cost"]):
@@ -676,7 +675,7 @@ def bench_calibration(args, env, name, scale, steps, warmup, light=False):
             issue = {"instructions_per_point": ipp, "achieved_ginst_per_s": ipp * n_loc / avg_s / 1e9,
                      "peak_ginst_per_s": issue_peak / 1e9, "frac": ipp * n_loc / avg_s / issue_peak,
                      "from_capture": mix.get("capture")}
-        roof = {"bound": "fp64", "kernel": "k_eval (= the evaluation phase of k_lm_persistent)",
+        roof = {"bound": "fp64", "kernel": "k_eval",
                 "achieved": fl / avg_s / 1e12, "peak": peak64, "unit": "TFLOP/s",
                 # headline fraction: executed FP64 instructions against the measured issue rate; the
                 # algorithmic figure (1012 FLOP / point) is kept beside it
@@ -692,7 +691,7 @@ def bench_calibration(args, env, name, scale, steps, warmup, light=False):
                 "fp64_issue": issue,
                 # the whole refinement as one launch: algorithmic work of all its sweeps / its duration
                 "whole_refinement": {
-                    "kernel": "k_lm_persistent" if tot_launch == steps else "per-launch pipeline",
+                    "kernel": "all kernels of the loop (k_eval, k_schur, k_backsub, k_cost inside the graph)",
                     "tflops_algorithmic": (tot_eval * FLOPS_PER_POINT[model] + tot_it * COST_FLOPS_PER_POINT) * n_loc
                                           / (tot_ms * 1e-3) / 1e12,
                     "frac_algorithmic": (tot_eval * FLOPS_PER_POINT[model] + tot_it * COST_FLOPS_PER_POINT) * n_loc

@@ -2,6 +2,9 @@
 // list, the per-iteration CUDA graph, the LM driver loop, NCCL plumbing for sharded views.
 #include <cuda_runtime.h>
 #include <dlfcn.h>
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
 #include <nccl.h>
 
 #include <algorithm>
@@ -437,15 +440,18 @@ extern "C" const char* calib_last_error(const calib_t* h) {
 // ---- detections held as per-view arrays: gather and upload, pipelined ---------------------------
 namespace {
 
-constexpr size_t kGatherChunk = (size_t)1 << 20;   // bytes per staged piece
-constexpr int kGatherThreads = 8;                   // at most; each with two staging slots
-constexpr int kGatherDefault = 4;                   // 4 x ~13 GB/s of memcpy keeps up with the PCIe copies; 8 measured slower
+constexpr size_t kGatherChunkMax = (size_t)4 << 20; // bytes per staged piece, at most
+constexpr int kGatherThreads = 8;                   // at most
+constexpr int kGatherSlots = 4;                     // staging slots per thread, at most
+constexpr size_t kGatherChunkDefault = (size_t)1 << 20;
+constexpr int kGatherSlotsDefault = 2;
+constexpr int kGatherDefault = 6;                   // with streaming stores 4 threads are gather-bound, 8 wait for PCIe; both ~1.6 ms at 62 MB
 
 struct GatherPool {                                 // per device; created on first use, kept
     std::mutex mu;
     char* pinned = nullptr;
     cudaStream_t stream[kGatherThreads] = {};
-    cudaEvent_t slot_free[kGatherThreads][2] = {};
+    cudaEvent_t slot_free[kGatherThreads][kGatherSlots] = {};
     cudaEvent_t done[kGatherThreads] = {};
     bool ok = false;
 };
@@ -453,26 +459,55 @@ GatherPool g_gather[64];
 
 cudaError_t gather_pool_init(GatherPool& g) {
     if (g.ok) return cudaSuccess;
-    cudaError_t e = cudaHostAlloc((void**)&g.pinned, kGatherThreads * 2 * kGatherChunk, cudaHostAllocPortable);
+    cudaError_t e = cudaHostAlloc((void**)&g.pinned, kGatherThreads * kGatherSlots * kGatherChunkMax, cudaHostAllocPortable);
     if (e != cudaSuccess) return e;
     for (int t = 0; t < kGatherThreads && e == cudaSuccess; ++t) {
         e = cudaStreamCreateWithFlags(&g.stream[t], cudaStreamNonBlocking);
-        for (int k = 0; k < 2 && e == cudaSuccess; ++k) e = cudaEventCreateWithFlags(&g.slot_free[t][k], cudaEventDisableTiming);
+        for (int k = 0; k < kGatherSlots && e == cudaSuccess; ++k) e = cudaEventCreateWithFlags(&g.slot_free[t][k], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&g.done[t], cudaEventDisableTiming);
     }
     g.ok = e == cudaSuccess;
     return e;
 }
 
+// memcpy with streaming (non-temporal) stores where the target has SSE2.  The staging slot is read next by
+// the GPU's DMA engine, not by this core: ordinary stores leave the lines dirty in this core's caches and every
+// DMA read then has to snoop them out, streaming stores put them in memory (measured, profiles/README.md).
+// The caller fences (_mm_sfence) before handing the slot to the copy.
+inline void copy_streaming(char* d, const char* s, size_t n) {
+#if defined(__SSE2__)
+    size_t head = (16 - ((uintptr_t)d & 15)) & 15;
+    if (head > n) head = n;
+    if (head) { memcpy(d, s, head); d += head; s += head; n -= head; }
+    for (; n >= 64; d += 64, s += 64, n -= 64) {
+        const __m128i a = _mm_loadu_si128((const __m128i*)s), b = _mm_loadu_si128((const __m128i*)(s + 16));
+        const __m128i c = _mm_loadu_si128((const __m128i*)(s + 32)), e = _mm_loadu_si128((const __m128i*)(s + 48));
+        _mm_stream_si128((__m128i*)d, a); _mm_stream_si128((__m128i*)(d + 16), b);
+        _mm_stream_si128((__m128i*)(d + 32), c); _mm_stream_si128((__m128i*)(d + 48), e);
+    }
+    for (; n >= 16; d += 16, s += 16, n -= 16) _mm_stream_si128((__m128i*)d, _mm_loadu_si128((const __m128i*)s));
+    if (n) memcpy(d, s, n);
+#else
+    memcpy(d, s, n);
+#endif
+}
+
 // Copies `bytes` bytes starting at byte `lo` of the concatenation of the views' arrays (stride bytes per
 // point) into dst.
-void gather_range(char* dst, const double* const* ptrs, const int64_t* offs, int64_t M, size_t stride, size_t lo, size_t bytes) {
+void gather_range(char* dst, const double* const* ptrs, const int64_t* offs, int64_t M, size_t stride, size_t lo, size_t bytes,
+                  bool streaming) {
     const size_t hi = lo + bytes;
     int64_t i = (std::upper_bound(offs, offs + M + 1, (int64_t)(lo / stride)) - offs) - 1;
     for (; i < M && (size_t)offs[i] * stride < hi; ++i) {
         const size_t a = std::max((size_t)offs[i] * stride, lo), b = std::min((size_t)offs[i + 1] * stride, hi);
-        if (b > a) memcpy(dst + (a - lo), (const char*)ptrs[i] + (a - (size_t)offs[i] * stride), b - a);
+        if (b <= a) continue;
+        const char* src = (const char*)ptrs[i] + (a - (size_t)offs[i] * stride);
+        if (streaming) copy_streaming(dst + (a - lo), src, b - a);
+        else memcpy(dst + (a - lo), src, b - a);
     }
+#if defined(__SSE2__)
+    if (streaming) _mm_sfence();
+#endif
 }
 
 // model points -> aos_model (N x 3), sensor points -> aos_sensor (N x 2), both device and ready to be
@@ -487,6 +522,16 @@ cudaError_t upload_views(int device, const int64_t* offs, int64_t M, const doubl
     if (e != cudaSuccess) return e;
     const size_t N = (size_t)offs[M];
     const size_t bytes_m = N * 24, bytes_s = N * 16;
+    static const size_t kGatherChunk = [] {
+        const char* ev = getenv("CALIB_GATHER_CHUNK_KB");
+        return ev ? std::max<size_t>(64 << 10, std::min(kGatherChunkMax, (size_t)atoi(ev) << 10)) : kGatherChunkDefault;
+    }();
+    static const int slots = [] {
+        const char* ev = getenv("CALIB_GATHER_SLOTS");
+        return ev ? std::max(1, std::min(kGatherSlots, atoi(ev))) : kGatherSlotsDefault;
+    }();
+    static const bool one_stream = getenv("CALIB_GATHER_ONE_STREAM") != nullptr;
+    static const bool streaming = [] { const char* ev = getenv("CALIB_GATHER_NT"); return ev ? atoi(ev) != 0 : true; }();
     const size_t cm = (bytes_m + kGatherChunk - 1) / kGatherChunk, cs = (bytes_s + kGatherChunk - 1) / kGatherChunk;
     const size_t nchunks = cm + cs;
     int T = kGatherDefault;
@@ -511,18 +556,20 @@ cudaError_t upload_views(int device, const int64_t* offs, int64_t M, const doubl
             const bool is_m = c < cm;
             const size_t lo = (is_m ? c : c - cm) * kGatherChunk;
             const size_t n = std::min(kGatherChunk, (is_m ? bytes_m : bytes_s) - lo);
-            char* slot = g.pinned + ((size_t)t * 2 + (k & 1)) * kGatherChunk;
+            const int sl = k % slots;
+            char* slot = g.pinned + ((size_t)t * kGatherSlots + sl) * kGatherChunkMax;
             auto ta = std::chrono::steady_clock::now();
-            r = cudaEventSynchronize(g.slot_free[t][k & 1]);   // the copy that last used this slot (any call) has left it
+            r = cudaEventSynchronize(g.slot_free[t][sl]);   // the copy that last used this slot (any call) has left it
             if (r != cudaSuccess) break;
             if (timing) { t_wait[t] += us_since(ta); ta = std::chrono::steady_clock::now(); }
-            gather_range(slot, is_m ? vm : vs, offs, M, is_m ? 24 : 16, lo, n);
+            gather_range(slot, is_m ? vm : vs, offs, M, is_m ? 24 : 16, lo, n, streaming);
             if (timing) { t_gather[t] += us_since(ta); ta = std::chrono::steady_clock::now(); }
-            r = cudaMemcpyAsync((char*)(is_m ? aos_model : aos_sensor) + lo, slot, n, cudaMemcpyHostToDevice, g.stream[t]);
-            if (r == cudaSuccess) r = cudaEventRecord(g.slot_free[t][k & 1], g.stream[t]);
+            cudaStream_t cs_ = g.stream[one_stream ? 0 : t];
+            r = cudaMemcpyAsync((char*)(is_m ? aos_model : aos_sensor) + lo, slot, n, cudaMemcpyHostToDevice, cs_);
+            if (r == cudaSuccess) r = cudaEventRecord(g.slot_free[t][sl], cs_);
             if (timing) t_issue[t] += us_since(ta);
         }
-        if (r == cudaSuccess) r = cudaEventRecord(g.done[t], g.stream[t]);
+        if (r == cudaSuccess) r = cudaEventRecord(g.done[t], g.stream[one_stream ? 0 : t]);
         if (r != cudaSuccess) err.store((int)r);
     };
     if (T <= 1) work(0);
@@ -807,8 +854,11 @@ extern "C" int calib_host_gather(void* dst, const void* const* srcs, const int64
         size_t i = (size_t)(std::upper_bound(off.begin(), off.end(), lo) - off.begin()) - 1;
         for (; i < (size_t)n && off[i] < hi; ++i) {
             const size_t a = std::max(off[i], lo), b = std::min(off[i + 1], hi);
-            if (b > a) memcpy((char*)dst + a, (const char*)srcs[i] + (a - off[i]), b - a);
+            if (b > a) copy_streaming((char*)dst + a, (const char*)srcs[i] + (a - off[i]), b - a);   // dst is staging for a DMA
         }
+#if defined(__SSE2__)
+        _mm_sfence();
+#endif
     };
     if (T == 1) { work(0); return CALIB_OK; }
     std::vector<std::thread> th;

@@ -145,6 +145,9 @@ def lib():
         "calib_batch_last_error": (ctypes.c_char_p, [_vp]),
         "calib_batch_lm_run": (c_int, [_vp, _d, c_int, c_dbl, c_dbl, c_dbl, c_dbl, _d,
                                        ctypes.POINTER(c_int), _d, _d]),
+        # device pointers as integers: (model, M, view_offsets_dev, N, model_pts_dev, sensor_pts_dev, P_dev, E_dev,
+        # device_id, cuda_stream)
+        "calib_cost_noalloc": (c_int, [c_int, c_i64, _vp, c_i64, _vp, _vp, _vp, _vp, c_int, _vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)

@@ -2040,3 +2040,4 @@ extern "C" int calib_debug_stamps(calib_t* h, const double* P, double lam, unsig
 #endif
 
 #include "calib_multi.inc"
+#include "calib_noalloc.inc"

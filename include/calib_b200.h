@@ -286,6 +286,27 @@ int calib_batch_lm_run(calib_batch_t* h, double* P_inout, int maxIters, double l
                        double lam_min, double lam_max, double err_min, double* sse_out,
                        int* iters_out, double* trace, double* device_ms);
 
+/* ---- allocation-free entry point --------------------------------------------------------------------
+ * NO counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Total reprojection error E(P) = sum |y_observed - project(P)|^2 (what calib_cost returns) of detections that are
+ * ALREADY ON THE DEVICE; every pointer is a DEVICE pointer of device_id:
+ *   view_offsets_dev  int64[M + 1]  first point of every view (view_offsets_dev[0] = 0, [M] = N), ragged / empty views allowed
+ *   model_pts_dev     double[N][3], sensor_pts_dev  double[N][2]   (the layout calib_create takes from the host)
+ *   P_dev             double[L + 6 M]  parameter vector (L = 10 radtan, 9 fisheye), E_dev  double[1]  the result
+ * The kernels are enqueued on cuda_stream (a cudaStream_t; NULL = the default stream) and the call returns without
+ * synchronising: E_dev is valid in stream order.  The call allocates nothing (no cudaMalloc / cudaFree / host
+ * allocation, no stream or event): its scratch -- view constants, per-block partial sums, the reduction's ticket --
+ * is one static device array of 206 336 bytes that every GPU loading the library holds until the process exits.
+ * Limit: M <= CALIB_NOALLOC_MAX_VIEWS (1024); more is refused with CALIB_E_ARG and a message (calib_last_error(NULL)).
+ * All calls on a GPU share that array: calls in stream order are independent (each rewrites what it reads and clears
+ * the ticket first), calls that OVERLAP on one GPU (two streams, two threads) race -- serialise them.
+ * Agrees with calib_cost to rounding (same per-point arithmetic, another summation order): 1e-12 relative. */
+#define CALIB_NOALLOC_MAX_VIEWS 1024
+int calib_cost_noalloc(int model, int64_t M, const int64_t* view_offsets_dev, int64_t N,
+                       const double* model_pts_dev, const double* sensor_pts_dev, const double* P_dev,
+                       double* E_dev, int device_id, void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

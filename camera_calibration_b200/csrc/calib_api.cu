@@ -2007,6 +2007,22 @@ extern "C" int calib_batch_lm_run(calib_batch_t* h, double* P_inout, int maxIter
 }
 
 #ifdef CALIB_STAMPS
+// latency-study builds only: cycle counters per phase of k_batch_lm, summed over the blocks of the runs since the
+// last call (the first call allocates them; out = kBatchPhases values)
+extern "C" int calib_batch_debug_phases(calib_batch_t* h, unsigned long long* out) {
+    if (!h) return bfail(nullptr, CALIB_E_ARG, "NULL handle");
+    BATCH_TRY(h, cudaSetDevice(h->device));
+    if (!h->dev.phase) {
+        BATCH_TRY(h, cudaMalloc((void**)&h->dev.phase, kBatchPhases * 8));
+        BATCH_TRY(h, cudaMemset(h->dev.phase, 0, kBatchPhases * 8));
+        for (int i = 0; i < kBatchPhases; ++i) out[i] = 0;
+        return CALIB_OK;
+    }
+    BATCH_TRY(h, cudaMemcpy(out, h->dev.phase, kBatchPhases * 8, cudaMemcpyDeviceToHost));
+    BATCH_TRY(h, cudaMemset(h->dev.phase, 0, kBatchPhases * 8));
+    return CALIB_OK;
+}
+
 // latency-study builds only: the persistent kernel's stamps of the last run, [2][kPStampPasses][kPStampSlots]
 extern "C" int calib_debug_pstamps(calib_t* h, unsigned long long* out) {
     RC(check_handle(h));

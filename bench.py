@@ -280,7 +280,9 @@ def reference_python_block(product=None, case="cfg1"):
         out["product_same_case"] = {
             "ms_per_refinement": ms, "iterations": int(iters), "sse": float(sse),
             "iterations_equal": bool(int(iters) == int(r["iterations"])),
-            "max_abs_param_diff": float(np.max(np.abs(np.asarray(P) - P_ref))),
+            # Euler angles (degrees) compared modulo 360
+            "max_abs_param_diff": float(np.max(np.minimum(np.abs(np.asarray(P) - P_ref),
+                                                          np.abs(np.abs(np.asarray(P) - P_ref) - 360.0)))),
             "sse_abs_diff": abs(float(sse) - float(r["sse"])),
             "speedup_by_time": 1e3 * r["refine_call_s"] / ms if ms else None}
     return out

@@ -19,7 +19,15 @@ def view_bounds(counts, world):
 
 
 def view_range(allDetections, world, rank):
+    """Views of `rank`.  Every rank computes the same bounds, so a split that would leave ANY rank without
+    views (more ranks than views, or all points in a few views) is refused on all ranks alike -- not by
+    calib_create on the empty rank alone while its peers wait in collectives.  (The single-process handle,
+    calib_multi_create, drops such ranks instead.)"""
     b = view_bounds([len(s) for s, m in allDetections], world)
+    empty = [r for r in range(world) if b[r + 1] <= b[r]]
+    if empty:
+        raise ValueError(f"view sharding over {world} ranks leaves rank(s) {empty} without views "
+                         f"({len(allDetections)} views): use fewer ranks")
     return b[rank], b[rank + 1]
 
 
@@ -65,16 +73,16 @@ def connect(prob, dist, transport="auto"):
         mine = torch.frombuffer(bytearray(prob.peer_export()), dtype=torch.uint8).to(dev)
         allh = [torch.empty_like(mine) for _ in range(world)]
         dist.all_gather(allh, mine)
-        ok = 1
+        ok, err = 1, None
         try:
             prob.peer_attach(world, rank, b"".join(bytes(t.cpu().numpy().tobytes()) for t in allh))
-        except Exception:
-            if transport == "peer":
-                raise
-            ok = 0
+        except Exception as e:       # every rank still takes part in the vote below: the others are entering it
+            ok, err = 0, e
         flag = torch.tensor([ok], dtype=torch.int32, device=dev)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
         got_peer = bool(flag.item())
+        if not got_peer and transport == "peer":
+            raise RuntimeError("peer-memory transport not available on every rank") from err
     if got_peer and transport != "nccl":
         prob.set_transport(2)
         return "peer"

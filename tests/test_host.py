@@ -184,3 +184,20 @@ def test_view_pointers_of_detection_lists():
     assert calibrate._view_pointers([(dets[0][0][:3], dets[0][1])]) is None
     wide = rs.rand(4, 6)
     assert calibrate._view_pointers([(dets[0][0], wide[:, :3])]) is None
+
+
+def test_view_range_refuses_empty_shards_on_every_rank():
+    """more ranks than views (or all points in few views): every rank must raise the same error before any
+    handle is created -- a rank that alone failed in calib_create would leave its peers in a collective"""
+    from camera_calibration_b200 import sharding
+    dets = [(np.zeros((n, 2)), np.zeros((n, 3))) for n in (6, 6, 6)]
+    for rank in range(3):
+        lo, hi = sharding.view_range(dets, 3, rank)
+        assert hi == lo + 1
+    for rank in range(4):
+        with pytest.raises(ValueError, match="without views"):
+            sharding.view_range(dets, 4, rank)
+    lopsided = [(np.zeros((n, 2)), np.zeros((n, 3))) for n in (1000, 1, 1)]
+    for rank in range(3):
+        with pytest.raises(ValueError, match="without views"):
+            sharding.view_range(lopsided, 3, rank)

@@ -918,7 +918,7 @@ void enqueue_eval(calib_handle* h, Launcher& ln) {
     const Dev& d = h->dev;
     cudaEvent_t a, b;
     ln.begin(&a, &b);
-    launch_iter(h, k_eval<MODEL>, d.ev_blocks, kBlockThreads, kEvalDynSmem, d);
+    launch_iter(h, k_eval<MODEL>, d.ev_blocks, kEvalThreads, kEvalDynSmem, d);
     ln.end(KEVAL, a, b);
     ln.count += 1;
 }
@@ -1309,8 +1309,8 @@ int lm_finish(calib_handle* h) {
         count += (int64_t)kernels_per_iteration(h) * h->h_state->n_pass;
     if (h->h_state->bar_abort) {
         char b[160];
-        snprintf(b, sizeof b, "a wait inside the kernels timed out (code %d: 1 grid barrier of the persistent kernel, 2 / 3 "
-                              "producer / consumer hand-off of the evaluation pass)", h->h_state->bar_abort);
+        snprintf(b, sizeof b, "a wait inside the kernels timed out (code %d: 1 grid barrier of the persistent kernel, 2 / 3 / 4 "
+                              "hand-off of the evaluation pass: chain / intrinsic-sums / view-sums warp)", h->h_state->bar_abort);
         return fail(h, CALIB_E_CUDA, b);
     }
     float ms = 0;

@@ -218,13 +218,14 @@ __device__ __forceinline__ void accum_BD(const PointOut<MODEL>& o, double (&acc)
 // point as in accum_BD (bit-identical); only the order in which the inputs are touched differs: the
 // six extrinsic column pairs are held, the left factors stream through two at a time, so that 14
 // input values are live at once instead of 26 beside the 87 sums.
+// (jslot[j * 32] = (ju,jv)[j]: the same slot, or the second ring of the pipelined pass.)
 template <int MODEL>
-__device__ __forceinline__ void accum_BD_ring(const double2* slot, double (&acc)[kNBD]) {
+__device__ __forceinline__ void accum_BD_ring2(const double2* slot, const double2* jslot, double (&acc)[kNBD]) {
     constexpr int ND = ModelTraits<MODEL>::ND, L = ModelTraits<MODEL>::L;
     using S = SlotsBD<L>;
     double ju[6], jv[6];
 #pragma unroll
-    for (int j = 0; j < 6; ++j) { const double2 t = slot[(2 + ND + j) * 32]; ju[j] = t.x; jv[j] = t.y; }
+    for (int j = 0; j < 6; ++j) { const double2 t = jslot[j * 32]; ju[j] = t.x; jv[j] = t.y; }
     {
         const double2 r = slot[1 * 32];                  // (ru, rv)
 #pragma unroll
@@ -253,6 +254,11 @@ __device__ __forceinline__ void accum_BD_ring(const double2* slot, double (&acc)
         for (int j = 0; j < 6; ++j)
             acc[S::B + (5 + a) * 6 + j] = fma(k.x, ju[j], fma(k.y, jv[j], acc[S::B + (5 + a) * 6 + j]));
     }
+}
+
+template <int MODEL>
+__device__ __forceinline__ void accum_BD_ring(const double2* slot, double (&acc)[kNBD]) {
+    accum_BD_ring2<MODEL>(slot, slot + (2 + ModelTraits<MODEL>::ND) * 32, acc);
 }
 
 // ---- a warp's sweep over its pieces ---------------------------------------------------------

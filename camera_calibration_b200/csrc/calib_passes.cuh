@@ -39,19 +39,12 @@ __device__ __forceinline__ PassCtx pass_ctx(const LmState& st) {
 }
 
 // ---- the fused evaluation pass ----------------------------------------------------------------
-// Producer / consumer warp pairs.  A point's 2 x (L+6) Jacobian rows feed 143 running sums (56 of
-// the intrinsic block A, g_c and the cost; 87 of B_v, D_v, g_v): more than one thread can hold.  The
-// first version swept the points twice with ONE warp (projection chain re-evaluated in the second
-// sweep: 416 FP64 instructions per point, 62 % of the FP64 issue rate because two warps per scheduler
-// cannot cover the ~60-deep dependent projection chain).  Here a PAIR of warps shares one sweep:
-//   producer   loads the point, runs point_eval once (the dependent chain), accumulates A, g_c, E in
-//              its registers and hands the 2 x (8 + ND) values the view blocks need to the consumer
-//              through a small ring in shared memory (one 16-byte slot per lane and value pair);
-//   consumer   accumulates B_v, D_v, g_v -- 144 independent FMAs per point, no chain, no global
-//              load -- and writes one row per piece.
-// 347 FP64 instructions per point instead of 416, and the scheduler always has the consumer's
-// independent FMAs to issue while the producer waits on its chain (pairs are warps w and w + 4: same
-// scheduler).  Per-lane accumulation order is that of the two-sweep version.
+// A point's 2 x (L+6) Jacobian rows feed 143 running sums (56 of the intrinsic block A, g_c and the cost;
+// 87 of B_v, D_v, g_v): more than one thread can hold.  History (profiles/README.md): one warp sweeping the
+// points twice (416 FP64 instructions per point, 60.3 us at cfg3); producer / consumer warp PAIRS sharing one
+// sweep through a ring in shared memory (356 instructions, detections read once, 61.8 us: bound by the
+// producer's instruction stream, csrc/experiments/calib_eval_pairs.cuh); now warp TRIPLES with re-balanced
+// registers (58.3 us), below.  Per-lane accumulation order is the same in all three: bit-identical results.
 constexpr int kEvalPairs = kBlockWarps / 2;
 constexpr int kEvalStages = 4;
 template <int MODEL> struct EvalRing {
@@ -99,94 +92,126 @@ __device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-// Block *vbp of the evaluation pass (pairs vb * 4 .. vb * 4 + 3 of the partition, rec = the record of
-// this warp's pair) at the point in parameter buffer `cur`: writes the piece rows of its pairs and row
-// vb of partA / partE.  vbp points to shared memory written before the call (not necessarily
-// synchronised: it is read after the barriers below) -- the index is needed after the sweep only and
-// must not cost a register inside it.  Called by all threads of a block; ends without a barrier after
-// its last shared-memory reads.  The ring lives in dynamic shared memory (kEvalDynSmem).
+// ---- warp triples with re-balanced registers ---------------------------------------------------------
+// ncu's source sampling of the pair kernel (profiles/r2f): one 32-point step took 1 570 cycles, the producer --
+// dependent projection chain AND the 57 sums of the intrinsic block, 352 instructions -- issued during 22 % of
+// them while the consumer slept on the hand-off.  Here the chain is a warp's ONLY work:
+//   P    (warps 0-3)   loads the point, runs point_eval, writes the hand-off slot -- no running sums;
+//   CA   (warps 4-7)   A, g_c and the cost (56 sums + 1) from pairs 0 .. 1+ND of the slot;
+//   CB   (warps 8-11)  B_v, D_v, g_v (87 sums) from all 8+ND pairs, one row per piece.
+// Warps t, t+4, t+8 share a scheduler and one ring (full: 1 arrival, empty: 2).  Three warps per scheduler
+// hold 168 registers each at launch; `setmaxnreg` moves them to where the sums live (radtan: P 112, CA 160,
+// CB 232; ptxas allocates per region, USETMAXREG in SASS; no spill).  A step now takes ~1 200 cycles
+// (profiles/r4c_eval3_ncu.md): P still bounds it -- 248 instructions at one issue per ~5 cycles (fixed-latency
+// dependencies 34 % of its samples) -- with the FP64 pipe 59 % busy.  Measured and rejected on top of this
+// (profiles/r4b, r4e): cutting the chain in two (P -> CA -> CB pipeline, experiments/calib_eval_pipeline.cuh:
+// slower, every warp of the scheduler then waits on the pipe), two steps per loop trip with swapped point
+// buffers (no gain), an L2 prefetch three steps ahead (-10 us on cold data, +1.4 us on L2-resident data).
+constexpr int kEvalThreads = 384;
+// per model: radtan carries 57 sums in CA and a shorter chain in P, fisheye 46 sums and the atan chain (no spill in either)
+template <int MODEL> struct EvalRegs;
+template <> struct EvalRegs<0> { static constexpr int P = 112, A = 160, B = 232; };
+template <> struct EvalRegs<1> { static constexpr int P = 128, A = 144, B = 232; };
+template <int N> __device__ __forceinline__ void reg_release() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
+template <int N> __device__ __forceinline__ void reg_acquire() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
+// from the 168 registers a thread of a 384-thread block starts with (dec above / inc below the current count is illegal)
+template <int N> __device__ __forceinline__ void reg_set() { if constexpr (N > 168) reg_acquire<N>(); else reg_release<N>(); }
+
 template <int MODEL>
-__device__ __forceinline__ void eval_block(const Dev& d, EvalSmem& sm, const volatile int* vbp, int cur, const WarpRec& rec) {
+__device__ __forceinline__ void accum_A_ring(const double2* slot, double (&acc)[kNA], double& e) {
+    constexpr int ND = ModelTraits<MODEL>::ND;
+    PointOut<MODEL> o;
+    { const double2 t = slot[0 * 32]; o.xd = t.x; o.yd = t.y; }
+    { const double2 t = slot[1 * 32]; o.ru = t.x; o.rv = t.y; }
+#pragma unroll
+    for (int a = 0; a < ND; ++a) { const double2 t = slot[(2 + a) * 32]; o.ku[a] = t.x; o.kv[a] = t.y; }
+    accum_A<MODEL>(o, acc, e);
+}
+
+template <int MODEL>
+__global__ void __launch_bounds__(kEvalThreads, 1) k_eval(Dev d) {
     using T = ModelTraits<MODEL>;
     constexpr int L = T::L, ND = T::ND, S = kEvalStages;
-    const int tid = tid_now();
+    const int tid = threadIdx.x;
     const int lane = tid & 31, warp = tid >> 5;
-    const int pair = warp & (kEvalPairs - 1);
-    const bool producer = warp < kEvalPairs;
-    EvalRing<MODEL>& ring = reinterpret_cast<EvalRing<MODEL>*>(dyn_smem)[pair];
-    unsigned long long* full = sm.full[pair];
-    unsigned long long* empty = sm.empty[pair];
-    STAMP(d, 0, 0);
+    const int trip = warp & (kEvalPairs - 1);
+    const int role = warp >> 2;                    // 0: P, 1: CA, 2: CB (warp-group uniform: setmaxnreg needs that)
+    const int w = blockIdx.x * kEvalPairs + trip;
+    WarpRec rec;
+    rec.p0 = rec.p1 = 0;
+    if (w < d.ev_warps) rec = d.ev_rec[w];
+    const LmState* st = d.st;
+    if (st->done || !st->need_eval) return;
+    __shared__ EvalSmem sm;
+    const int cur = st->cur;
+    EvalRing<MODEL>& ring = reinterpret_cast<EvalRing<MODEL>*>(dyn_smem)[trip];
+    unsigned long long* full = sm.full[trip];
+    unsigned long long* empty = sm.empty[trip];
     if (tid < L) sm.sc[tid] = d.Pbuf[(long long)cur * d.K + tid];
-    if (tid < kEvalPairs * S) { mbar_init(&sm.full[0][0] + tid, 1); mbar_init(&sm.empty[0][0] + tid, 1); }
+    if (tid < kEvalPairs * S) { mbar_init(&sm.full[0][0] + tid, 1); mbar_init(&sm.empty[0][0] + tid, 2); }
     if (tid == 0) mbar_fence_init();
     __syncthreads();
     const int p0 = rec.p0, p1 = rec.p1;
-    if (producer) {
-        // ---- producer: projection chain, A / g_c / E, hand-off
+    if (role == 0) {
+        // ---- P: the projection chain and the hand-off, nothing else
+        reg_release<EvalRegs<MODEL>::P>();
+        if (p0 >= p1) return;
+        const ViewC* views = d.views + (long long)cur * d.M;
+        Piece pc = rec.first;
+        Pt pn;
+        if (lane < pc.count) load_point(d, (long long)pc.start + lane, pn);
+        double vn = 0.0;
+        if (lane < kViewDoubles) vn = reinterpret_cast<const double*>(views + pc.view)[lane];
+        unsigned k = 0;                              // hand-offs so far
+        for (int pi = p0; pi < p1; ++pi) {
+            const bool has_next = pi + 1 < p1;
+            Piece nxt = pc;
+            if (has_next) nxt = d.ev_piece[pi + 1];
+            // the consumers never read sview: only this warp's own steps of the previous piece must be done
+            __syncwarp();
+            if (lane < kViewDoubles) reinterpret_cast<double*>(&sm.sview[trip])[lane] = vn;
+            __syncwarp();
+            if (has_next && lane < kViewDoubles) vn = reinterpret_cast<const double*>(views + nxt.view)[lane];
+            const int nsteps = (pc.count + 31) >> 5;
+            int idx = pc.start + lane;       // point indices fit 32 bits (Piece::start is an int)
+            int left = pc.count - lane;              // > 0: this lane has a point in the current step
+            // one step: the point in `p` is evaluated and handed off, the next one is fetched into `nx`
+            auto step = [&](const Pt& p, Pt& nx, bool last) {
+                const bool valid = left > 0;
+                left -= 32;
+                idx += 32;
+                if (!last) { if (left > 0) load_point(d, (long long)idx, nx); }
+                else if (has_next && lane < nxt.count) load_point(d, (long long)nxt.start + lane, nx);
+                const unsigned s = k % S;
+                if (k >= S) mbar_wait_guarded(&empty[s], ((k / S) - 1u) & 1u, d.st, 0);
+                if (valid) {
+                    PointOut<MODEL> o;
+                    point_eval<MODEL, true, true>(sm.sc, sm.sview[trip], p.X, p.Y, p.Z, p.U, p.V, o);
+                    double2* slot = &ring.v[s][0][lane];
+#pragma unroll
+                    for (int j = 0; j < 6; ++j) slot[(2 + ND + j) * 32] = make_double2(o.ju[j], o.jv[j]);
+                    slot[0 * 32] = make_double2(o.xd, o.yd);
+                    slot[1 * 32] = make_double2(o.ru, o.rv);
+#pragma unroll
+                    for (int a = 0; a < ND; ++a) slot[(2 + a) * 32] = make_double2(o.ku[a], o.kv[a]);
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&full[s]);
+                ++k;
+            };
+            for (int sidx = 0; sidx < nsteps; ++sidx) {
+                const Pt p = pn;
+                step(p, pn, sidx + 1 == nsteps);
+            }
+            pc = nxt;
+        }
+    } else if (role == 1) {
+        // ---- CA: intrinsic block, its right-hand side, the cost; then the block's row of partA / partE
+        reg_release<EvalRegs<MODEL>::A>();
         double acc[kNA];
 #pragma unroll
         for (int i = 0; i < kNA; ++i) acc[i] = 0.0;
         double e = 0.0;
-        if (p0 < p1) {
-            const ViewC* views = d.views + (long long)cur * d.M;
-            Piece pc = rec.first;
-            Pt pn;
-            if (lane < pc.count) load_point(d, (long long)pc.start + lane, pn);
-            double vn = 0.0;
-            if (lane < kViewDoubles) vn = reinterpret_cast<const double*>(views + pc.view)[lane];
-            int k = 0;                                   // hand-offs so far
-            for (int pi = p0; pi < p1; ++pi) {
-                const bool has_next = pi + 1 < p1;
-                Piece nxt = pc;
-                if (has_next) nxt = d.ev_piece[pi + 1];
-                __syncwarp();
-                if (lane < kViewDoubles) reinterpret_cast<double*>(&sm.sview[pair])[lane] = vn;
-                __syncwarp();
-                if (has_next && lane < kViewDoubles) vn = reinterpret_cast<const double*>(views + nxt.view)[lane];
-                const int nsteps = (pc.count + 31) >> 5;
-                long long idx = (long long)pc.start + lane;
-                int left = pc.count - lane;              // > 0: this lane has a point in the current step
-                for (int sidx = 0; sidx < nsteps; ++sidx) {
-                    const Pt p = pn;
-                    const bool valid = left > 0;
-                    left -= 32;
-                    idx += 32;
-                    if (sidx + 1 < nsteps) { if (left > 0) load_point(d, idx, pn); }
-                    else if (has_next && lane < nxt.count) load_point(d, (long long)nxt.start + lane, pn);
-                    // the stage is normally free long before (the consumer has less to do per point)
-                    const int s = k % S;
-                    if (k >= S) mbar_wait_guarded(&empty[s], (unsigned)((k / S) - 1) & 1u, d.st, 0);
-                    PointOut<MODEL> o;
-                    if (valid) {
-                        point_eval<MODEL, true, true>(sm.sc, sm.sview[pair], p.X, p.Y, p.Z, p.U, p.V, o);
-                        double2* slot = &ring.v[s][0][lane];     // hand-off first: the extrinsic columns die here
-#pragma unroll
-                        for (int j = 0; j < 6; ++j) slot[(2 + ND + j) * 32] = make_double2(o.ju[j], o.jv[j]);
-                        slot[0 * 32] = make_double2(o.xd, o.yd);
-                        slot[1 * 32] = make_double2(o.ru, o.rv);
-#pragma unroll
-                        for (int a = 0; a < ND; ++a) slot[(2 + a) * 32] = make_double2(o.ku[a], o.kv[a]);
-                    }
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&full[s]);
-                    if (valid) accum_A<MODEL>(o, acc, e);
-                    ++k;
-                }
-                pc = nxt;
-            }
-        }
-        STAMP(d, 0, 1);
-        warp_reduce_scatter<kNA>(acc, lane);
-        e = warp_sum(e);
-        sm.sred[pair][2 * lane] = acc[0];
-        sm.sred[pair][2 * lane + 1] = acc[1];
-        if (lane == 0) sm.sE[pair] = e;
-    } else {
-        // ---- consumer: B_v, D_v, g_v -- one row of kNBD slots per piece
-        double acc[kNBD];
-#pragma unroll
-        for (int i = 0; i < kNBD; ++i) acc[i] = 0.0;
         if (p0 < p1) {
             Piece pc = rec.first;
             int k = 0;
@@ -201,54 +226,66 @@ __device__ __forceinline__ void eval_block(const Dev& d, EvalSmem& sm, const vol
                     left -= 32;
                     const int s = k % S;
                     mbar_wait_guarded(&full[s], (unsigned)(k / S) & 1u, d.st, 1);
-                    if (valid) {
-                        accum_BD_ring<MODEL>(&ring.v[s][0][lane], acc);
-                    }
+                    if (valid) accum_A_ring<MODEL>(&ring.v[s][0][lane], acc, e);
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&empty[s]);
                     ++k;
                 }
-                warp_reduce_scatter<kNBD>(acc, lane);
-                double* row = d.partBD + (long long)pi * kNBD + lane * (kNBD / 32);
-#pragma unroll
-                for (int j = 0; j < kNBD / 32; ++j) row[j] = acc[j];
-#pragma unroll
-                for (int i = 0; i < kNBD; ++i) acc[i] = 0.0;
                 pc = nxt;
             }
         }
-        STAMP(d, 0, 2);
-    }
-    __syncthreads();
-    STAMP(d, 0, 3);
-    const int vb = *vbp;
-    if (tid < kNA) {
-        double s = sm.sred[0][tid];
+        warp_reduce_scatter<kNA>(acc, lane);
+        e = warp_sum(e);
+        sm.sred[trip][2 * lane] = acc[0];
+        sm.sred[trip][2 * lane + 1] = acc[1];
+        if (lane == 0) sm.sE[trip] = e;
+        asm volatile("bar.sync 1, 128;" ::: "memory");       // the four CA warps
+        const int t = tid - 128;
+        if (t < kNA) {
+            double s = sm.sred[0][t];
 #pragma unroll
-        for (int k = 1; k < kEvalPairs; ++k) s += sm.sred[k][tid];
-        d.partA[(long long)vb * kNA + tid] = s;
-    } else if (tid == kNA) {
-        double s = sm.sE[0];
+            for (int q = 1; q < kEvalPairs; ++q) s += sm.sred[q][t];
+            d.partA[(long long)blockIdx.x * kNA + t] = s;
+        } else if (t == kNA) {
+            double s = sm.sE[0];
 #pragma unroll
-        for (int k = 1; k < kEvalPairs; ++k) s = __dadd_rn(s, sm.sE[k]);
-        d.partE[vb] = s;
+            for (int q = 1; q < kEvalPairs; ++q) s = __dadd_rn(s, sm.sE[q]);
+            d.partE[blockIdx.x] = s;
+        }
+    } else {
+        // ---- CB: B_v, D_v, g_v -- one row of kNBD slots per piece
+        reg_acquire<EvalRegs<MODEL>::B>();
+        double acc[kNBD];
+#pragma unroll
+        for (int i = 0; i < kNBD; ++i) acc[i] = 0.0;
+        if (p0 >= p1) return;
+        Piece pc = rec.first;
+        int k = 0;
+        for (int pi = p0; pi < p1; ++pi) {
+            const bool has_next = pi + 1 < p1;
+            Piece nxt = pc;
+            if (has_next) nxt = d.ev_piece[pi + 1];
+            const int nsteps = (pc.count + 31) >> 5;
+            int left = pc.count - lane;
+            for (int sidx = 0; sidx < nsteps; ++sidx) {
+                const bool valid = left > 0;
+                left -= 32;
+                const int s = k % S;
+                mbar_wait_guarded(&full[s], (unsigned)(k / S) & 1u, d.st, 2);
+                if (valid) accum_BD_ring<MODEL>(&ring.v[s][0][lane], acc);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&empty[s]);
+                ++k;
+            }
+            warp_reduce_scatter<kNBD>(acc, lane);
+            double* row = d.partBD + (long long)pi * kNBD + lane * (kNBD / 32);
+#pragma unroll
+            for (int j = 0; j < kNBD / 32; ++j) row[j] = acc[j];
+#pragma unroll
+            for (int i = 0; i < kNBD; ++i) acc[i] = 0.0;
+            pc = nxt;
+        }
     }
-    STAMP(d, 0, 4);
-}
-
-template <int MODEL>
-__global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
-    const int pair = (threadIdx.x >> 5) & (kEvalPairs - 1);
-    const int w = blockIdx.x * kEvalPairs + pair;
-    WarpRec rec;                       // issued together with the state load below: one round trip
-    rec.p0 = rec.p1 = 0;
-    if (w < d.ev_warps) rec = d.ev_rec[w];
-    const LmState* st = d.st;
-    if (st->done || !st->need_eval) return;
-    __shared__ EvalSmem sm;
-    __shared__ int s_vb;
-    if (threadIdx.x == 0) s_vb = blockIdx.x;
-    eval_block<MODEL>(d, sm, &s_vb, st->cur, rec);
 }
 
 // ---- accept / reject, lambda update, termination: src/calibrate.py:155-168 ------------------

@@ -33,6 +33,7 @@
 // bounded so it fails with CALIB_E_CUDA instead of hanging).
 #pragma once
 #include "../calib_solve.cuh"
+#include "calib_eval_pairs.cuh"
 
 namespace calib {
 

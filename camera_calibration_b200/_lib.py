@@ -83,6 +83,7 @@ def lib():
         "calib_create": (c_int, [ctypes.POINTER(_vp), c_int, c_i64, _i64, _d, _d, c_int]),
         "calib_create_from_views": (c_int, [ctypes.POINTER(_vp), c_int, c_i64, _i64, _vp, _vp, c_int]),
         "calib_destroy": (None, [_vp]),
+        "calib_trim": (c_int, [c_int]),
         "calib_num_params": (c_i64, [_vp]),
         "calib_num_points": (c_i64, [_vp]),
         "calib_set_segment": (c_int, [_vp, c_int]),

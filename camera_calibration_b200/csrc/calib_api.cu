@@ -33,12 +33,57 @@ using namespace calib;
 
 static thread_local std::string g_last_error;
 
-// Scratch buffers of one call: stream-ordered allocations from the device pool (which keeps what is
-// freed, pool_keep_memory), so a call costs no cudaMalloc / cudaFree.
+// All device memory of the library comes from ONE stream-ordered pool per device that the library owns
+// (not the device's default pool: its settings belong to the process, e.g. to a co-resident torch).  The pool
+// keeps what is freed -- creating the next problem costs no cudaMalloc -- until calib_trim(device) hands the
+// unused part back to the driver.
+static std::mutex g_pool_mu;
+static cudaMemPool_t g_pool[64] = {};
+static cudaError_t lib_pool(int device, cudaMemPool_t* out) {
+    std::lock_guard<std::mutex> lk(g_pool_mu);
+    if (device < 0 || device >= 64) return cudaErrorInvalidDevice;
+    if (!g_pool[device]) {
+        cudaMemPoolProps props;
+        memset(&props, 0, sizeof props);
+        props.allocType = cudaMemAllocationTypePinned;
+        props.handleTypes = cudaMemHandleTypeNone;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = device;
+        cudaMemPool_t pool = nullptr;
+        cudaError_t e = cudaMemPoolCreate(&pool, &props);
+        if (e != cudaSuccess) return e;
+        uint64_t thr = UINT64_MAX;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+        g_pool[device] = pool;
+    }
+    *out = g_pool[device];
+    return cudaSuccess;
+}
+// stream-ordered allocation on `device` (the device of `stream`)
+static cudaError_t lib_malloc_async(void** p, size_t bytes, cudaStream_t stream, int device) {
+    cudaMemPool_t pool;
+    cudaError_t e = lib_pool(device, &pool);
+    if (e != cudaSuccess) return e;
+    return cudaMallocFromPoolAsync(p, bytes, pool, stream);
+}
+
+extern "C" int calib_trim(int device) {
+    cudaMemPool_t pool = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_pool_mu);
+        if (device < 0 || device >= 64) return CALIB_E_ARG;
+        pool = g_pool[device];
+    }
+    if (!pool) return CALIB_OK;                  // nothing was ever allocated on that device
+    return cudaMemPoolTrimTo(pool, 0) == cudaSuccess ? CALIB_OK : CALIB_E_CUDA;
+}
+
+// Scratch buffers of one call: stream-ordered allocations from the library's pool, so a call costs no
+// cudaMalloc / cudaFree.
 template <typename T>
-static cudaError_t dalloc(std::vector<void*>& pool, T** p, size_t count, cudaStream_t stream) {
+static cudaError_t dalloc(std::vector<void*>& pool, T** p, size_t count, cudaStream_t stream, int device) {
     void* q = nullptr;
-    cudaError_t e = cudaMallocAsync(&q, std::max<size_t>(count, 1) * sizeof(T), stream);
+    cudaError_t e = lib_malloc_async(&q, std::max<size_t>(count, 1) * sizeof(T), stream, device);
     if (e == cudaSuccess) { pool.push_back(q); *p = (T*)q; }
     return e;
 }
@@ -157,7 +202,7 @@ bool nccl_load() {
     return g_nccl.ok;
 }
 
-// Bump allocator over one stream-ordered device allocation (cudaMallocAsync: the pool keeps the
+// Bump allocator over one stream-ordered device allocation (lib_malloc_async: the library's pool keeps the
 // memory of a destroyed handle, so creating the next problem does not pay for cudaMalloc again).
 struct Arena {
     size_t bytes = 0;
@@ -170,18 +215,6 @@ struct Arena {
     template <typename T> T* at(size_t off) const { return reinterpret_cast<T*>(base + off); }
 };
 
-void pool_keep_memory(int device) {
-    static std::mutex mu;
-    static bool done[64] = {false};
-    std::lock_guard<std::mutex> lk(mu);
-    if (device < 0 || device >= 64 || done[device]) return;
-    cudaMemPool_t pool;
-    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
-        uint64_t thr = UINT64_MAX;
-        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
-    }
-    done[device] = true;
-}
 }  // namespace
 
 // Streams, events and the page-locked state block are expensive to create (cudaMallocHost takes
@@ -392,7 +425,7 @@ static int build_tasks(calib_handle* h, int seg, bool sync_now = true) {
     const size_t o_pA = a.reserve<double>((size_t)d.ev_blocks * kNA), o_pE = a.reserve<double>(d.ev_blocks);
     const size_t o_pBD = a.reserve<double>((size_t)std::max(d.ev_pieces, 1) * kNBD);
     const size_t o_pW = a.reserve<double>((size_t)d.sc_groups * kJMax * kNBD), o_pC = a.reserve<double>((size_t)d.co_blocks * kJMax);
-    CUDA_TRY(h, cudaMallocAsync(&h->arena_part, a.bytes, h->stream));
+    CUDA_TRY(h, lib_malloc_async((void**)&h->arena_part, a.bytes, h->stream, h->device));
     a.base = (char*)h->arena_part;
     // one upload for the five index tables
     std::vector<char>& meta = h->meta_host;      // stays alive until the stream has been synchronised
@@ -658,7 +691,6 @@ static int create_impl(calib_t** out, int model, int64_t M, const int64_t* view_
     std::function<cudaError_t()> repack;
 #define TRY_(call) do { int rc__ = [&]() -> int { CUDA_TRY(h, call); return 0; }(); if (rc__) { g_last_error = h->err; return bail(rc__); } } while (0)
     TRY_(cudaSetDevice(device_id));
-    pool_keep_memory(device_id);
     TRY_(device_func_attributes(device_id));
     TRY_(cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, device_id));
     { int rc = ctx_acquire(h); if (rc) { g_last_error = h->err; return bail(rc); } }
@@ -680,7 +712,7 @@ static int create_impl(calib_t** out, int model, int64_t M, const int64_t* view_
         const size_t o_trace = a.reserve<double>(20 * kTraceIters);     // trace rows, then the parameter trace
         const size_t zero_from = o_P, zero_bytes = a.bytes - o_P;
         const size_t o_aos = a.reserve<double>(5 * n);     // upload staging, AoS as the caller holds it
-        TRY_(cudaMallocAsync(&h->arena_fixed, a.bytes, h->stream));
+        TRY_(lib_malloc_async((void**)&h->arena_fixed, a.bytes, h->stream, h->device));
         a.base = (char*)h->arena_fixed;
         double* soa = a.at<double>(o_soa);
         d.X = soa; d.Y = soa + n; d.Z = soa + 2 * n; d.U = soa + 3 * n; d.V = soa + 4 * n;
@@ -1418,10 +1450,10 @@ int debug_point(calib_handle* h, const double* P, double* y, double* r, double* 
     const size_t N = (size_t)std::max<int64_t>(h->N, 1);
     double *dy = nullptr, *dr = nullptr, *dJc = nullptr, *dJv = nullptr;
     std::vector<void*> tmp;
-    if (y) CUDA_TRY(h, dalloc(tmp, &dy, 2 * N, h->stream));
-    if (r) CUDA_TRY(h, dalloc(tmp, &dr, 2 * N, h->stream));
-    if (Jc) CUDA_TRY(h, dalloc(tmp, &dJc, 2 * N * h->L, h->stream));
-    if (Jv) CUDA_TRY(h, dalloc(tmp, &dJv, 12 * N, h->stream));
+    if (y) CUDA_TRY(h, dalloc(tmp, &dy, 2 * N, h->stream, h->device));
+    if (r) CUDA_TRY(h, dalloc(tmp, &dr, 2 * N, h->stream, h->device));
+    if (Jc) CUDA_TRY(h, dalloc(tmp, &dJc, 2 * N * h->L, h->stream, h->device));
+    if (Jv) CUDA_TRY(h, dalloc(tmp, &dJv, 12 * N, h->stream, h->device));
     if (h->model == 0) launch_debug_point<0>(h, dy, dr, dJc, dJv);
     else launch_debug_point<1>(h, dy, dr, dJc, dJv);
     int rc = sync(h);
@@ -1493,10 +1525,10 @@ extern "C" int calib_eval_normal_equations(calib_t* h, const double* P, double* 
     const size_t M = (size_t)h->M;
     double *dA = nullptr, *dB = nullptr, *dD = nullptr, *dg = nullptr;
     std::vector<void*> tmp;
-    CUDA_TRY(h, dalloc(tmp, &dA, (size_t)L * L, h->stream));
-    CUDA_TRY(h, dalloc(tmp, &dB, M * L * 6, h->stream));
-    CUDA_TRY(h, dalloc(tmp, &dD, M * 36, h->stream));
-    CUDA_TRY(h, dalloc(tmp, &dg, (size_t)h->K, h->stream));
+    CUDA_TRY(h, dalloc(tmp, &dA, (size_t)L * L, h->stream, h->device));
+    CUDA_TRY(h, dalloc(tmp, &dB, M * L * 6, h->stream, h->device));
+    CUDA_TRY(h, dalloc(tmp, &dD, M * 36, h->stream, h->device));
+    CUDA_TRY(h, dalloc(tmp, &dg, (size_t)h->K, h->stream, h->device));
     const int nb = (int)((h->M + 127) / 128);
     if (h->model == 0) k_debug_unpack<0><<<nb, 128, 0, h->stream>>>(h->dev, dA, dB, dD, dg);
     else k_debug_unpack<1><<<nb, 128, 0, h->stream>>>(h->dev, dA, dB, dD, dg);
@@ -1737,10 +1769,10 @@ extern "C" int calib_refine_homographies(calib_t* h, double* H_inout, int maxIte
     double *d_H = nullptr, *d_tr = nullptr;
     int* d_it = nullptr;
     int rc = [&]() -> int {
-        CUDA_TRY(h, dalloc(tmp, &d_offs, M + 1, h->stream));
-        CUDA_TRY(h, dalloc(tmp, &d_H, M * 9, h->stream));
-        CUDA_TRY(h, dalloc(tmp, &d_it, M, h->stream));
-        if (trace) CUDA_TRY(h, dalloc(tmp, &d_tr, M * (size_t)maxIters * 4, h->stream));
+        CUDA_TRY(h, dalloc(tmp, &d_offs, M + 1, h->stream, h->device));
+        CUDA_TRY(h, dalloc(tmp, &d_H, M * 9, h->stream, h->device));
+        CUDA_TRY(h, dalloc(tmp, &d_it, M, h->stream, h->device));
+        if (trace) CUDA_TRY(h, dalloc(tmp, &d_tr, M * (size_t)maxIters * 4, h->stream, h->device));
         static_assert(sizeof(long long) == sizeof(int64_t), "int64 layout");
         CUDA_TRY(h, cudaMemcpyAsync(d_offs, h->view_offsets.data(), (M + 1) * 8, cudaMemcpyHostToDevice, h->stream));
         CUDA_TRY(h, cudaMemcpyAsync(d_H, H_inout, M * 72, cudaMemcpyHostToDevice, h->stream));
@@ -1771,9 +1803,9 @@ int linear_call(calib_handle* h, int which, const double* A9, const double* W12,
     int rc = [&]() -> int {
         long long* d_offs = nullptr;
         double *d0 = nullptr, *d1 = nullptr, *dA = nullptr, *dW = nullptr;
-        CUDA_TRY(h, dalloc(tmp, &d_offs, M + 1, h->stream));
-        CUDA_TRY(h, dalloc(tmp, &d0, M * n0, h->stream));
-        if (n1) CUDA_TRY(h, dalloc(tmp, &d1, M * n1, h->stream));
+        CUDA_TRY(h, dalloc(tmp, &d_offs, M + 1, h->stream, h->device));
+        CUDA_TRY(h, dalloc(tmp, &d0, M * n0, h->stream, h->device));
+        if (n1) CUDA_TRY(h, dalloc(tmp, &d1, M * n1, h->stream, h->device));
         CUDA_TRY(h, cudaMemcpyAsync(d_offs, h->view_offsets.data(), (M + 1) * 8, cudaMemcpyHostToDevice, h->stream));
         LinDev d;
         memset(&d, 0, sizeof d);
@@ -1783,14 +1815,14 @@ int linear_call(calib_handle* h, int which, const double* A9, const double* W12,
         if (which == 0 || which == 2) {
             if (which == 0) { d.gram = d0; d.norm = d1; }
             else {          // the homographies are what leaves the device; Gram sums and normalisations stay
-                CUDA_TRY(h, dalloc(tmp, &d.gram, M * kGramN, h->stream));
-                CUDA_TRY(h, dalloc(tmp, &d.norm, M * kNormN, h->stream));
+                CUDA_TRY(h, dalloc(tmp, &d.gram, M * kGramN, h->stream, h->device));
+                CUDA_TRY(h, dalloc(tmp, &d.norm, M * kNormN, h->stream, h->device));
                 d.Hdlt = d0;
             }
             k_dlt_gram<<<blocks, kBlockThreads, 0, h->stream>>>(d);
         } else {
-            CUDA_TRY(h, dalloc(tmp, &dA, 9, h->stream));
-            CUDA_TRY(h, dalloc(tmp, &dW, M * 12, h->stream));
+            CUDA_TRY(h, dalloc(tmp, &dA, 9, h->stream, h->device));
+            CUDA_TRY(h, dalloc(tmp, &dW, M * 12, h->stream, h->device));
             CUDA_TRY(h, cudaMemcpyAsync(dA, A9, 72, cudaMemcpyHostToDevice, h->stream));
             CUDA_TRY(h, cudaMemcpyAsync(dW, W12, M * 96, cudaMemcpyHostToDevice, h->stream));
             d.A = dA; d.W = dW; d.drows = d0;
@@ -1931,13 +1963,12 @@ extern "C" int calib_batch_create(calib_batch_t** out, int model, int64_t n_prob
     double *soa = nullptr, *aos = nullptr;
     long long *pv = nullptr, *vo = nullptr;
     {
-        pool_keep_memory(device_id);
-        Arena a;
+            Arena a;
         const size_t o_soa = a.reserve<double>(5 * n + 64), o_aos = a.reserve<double>(5 * n);
         const size_t o_pv = a.reserve<long long>((size_t)n_problems + 1), o_vo = a.reserve<long long>((size_t)total_views + 1);
         const size_t o_P = a.reserve<double>((size_t)h->total_params), o_sse = a.reserve<double>((size_t)n_problems);
         const size_t o_it = a.reserve<int>((size_t)n_problems);
-        TRYB_(cudaMallocAsync(&h->arena, a.bytes, h->stream));
+        TRYB_(lib_malloc_async((void**)&h->arena, a.bytes, h->stream, h->device));
         a.base = (char*)h->arena;
         soa = a.at<double>(o_soa); aos = a.at<double>(o_aos);
         pv = a.at<long long>(o_pv); vo = a.at<long long>(o_vo);
@@ -1977,7 +2008,7 @@ extern "C" int calib_batch_lm_run(calib_batch_t* h, double* P_inout, int maxIter
         if (need > h->trace_cap) {
             if (h->trace_dev) cudaFreeAsync(h->trace_dev, h->stream);
             h->trace_dev = nullptr; h->trace_cap = 0;
-            BATCH_TRY(h, cudaMallocAsync((void**)&h->trace_dev, need * 8, h->stream));
+            BATCH_TRY(h, lib_malloc_async((void**)&h->trace_dev, need * 8, h->stream, h->device));
             h->trace_cap = need;
         }
         BATCH_TRY(h, cudaMemsetAsync(h->trace_dev, 0, need * 8, h->stream));

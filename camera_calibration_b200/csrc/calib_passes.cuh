@@ -106,7 +106,8 @@ __device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
 // dependencies 34 % of its samples) -- with the FP64 pipe 59 % busy.  Measured and rejected on top of this
 // (profiles/r4b, r4e): cutting the chain in two (P -> CA -> CB pipeline, experiments/calib_eval_pipeline.cuh:
 // slower, every warp of the scheduler then waits on the pipe), two steps per loop trip with swapped point
-// buffers (no gain), an L2 prefetch three steps ahead (-10 us on cold data, +1.4 us on L2-resident data).
+// buffers (no gain), an L2 prefetch three steps ahead (-10 us on cold data, +1.4 us on L2-resident data), the
+// chain without its `valid` branch (lanes without a point computing on stale registers: 57.9 against 57.9 us).
 constexpr int kEvalThreads = 384;
 // per model: radtan carries 57 sums in CA and a shorter chain in P, fisheye 46 sums and the atan chain (no spill in either)
 template <int MODEL> struct EvalRegs;

@@ -62,6 +62,11 @@ int calib_create(calib_t** out, int model, int64_t M, const int64_t* view_offset
 int calib_create_from_views(calib_t** out, int model, int64_t M, const int64_t* counts,
                             const double* const* model_ptrs, const double* const* sensor_ptrs, int device_id);
 void calib_destroy(calib_t* h);
+/* Device memory of destroyed handles (and the scratch of the per-call entry points) stays in a stream-ordered
+ * pool that the library owns, one per device -- never the device's default pool -- so that the next calib_create
+ * pays no cudaMalloc.  calib_trim hands what is not in use back to the driver (e.g. before another framework in
+ * the process needs the memory).  No counterpart in the reference (its arrays are numpy's). */
+int calib_trim(int device_id);
 
 int64_t calib_num_params(const calib_t* h);  /* K = L + 6M */
 int64_t calib_num_points(const calib_t* h);  /* N */

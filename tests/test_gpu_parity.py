@@ -793,6 +793,36 @@ def test_many_handles_created_and_destroyed(golden):
     prob.close()
 
 
+def test_trim_returns_the_pool_and_the_library_goes_on(golden):
+    """The library's own memory pool (one per device, never the device's default pool) keeps what destroyed
+    handles free; calib_trim hands it back to the driver, with a live handle untouched and the next create
+    working as before.  The default pool's release threshold is what the process set it to (0 here)."""
+    import ctypes
+    from camera_calibration_b200 import _lib
+    L = _lib.lib()
+    g = golden("cfg2")
+    live = _problem(g)
+    ref = live.lm_run(g["P0"], 30)
+    for _ in range(3):
+        prob = _problem(g)
+        prob.lm_run(g["P0"], 5)
+        prob.close()
+    assert L.calib_trim(0) == 0
+    assert L.calib_trim(-1) != 0 and L.calib_trim(63) == 0        # bad index refused; unused device: nothing to do
+    again = live.lm_run(g["P0"], 30)                                # the live handle's memory was not trimmed
+    assert again[0] == ref[0] and np.array_equal(again[1], ref[1])
+    live.close()
+    prob = _problem(g)
+    assert prob.lm_run(g["P0"], 30)[0] == ref[0]
+    prob.close()
+    rt = ctypes.CDLL("libcudart.so.12")
+    pool = ctypes.c_void_p()
+    assert rt.cudaDeviceGetDefaultMemPool(ctypes.byref(pool), 0) == 0
+    thr = ctypes.c_uint64(123)
+    assert rt.cudaMemPoolGetAttribute(pool, 4, ctypes.byref(thr)) == 0     # cudaMemPoolAttrReleaseThreshold = 4
+    assert thr.value == 0
+
+
 def test_soak_repeats_bit_for_bit(golden):
     """Stand-in for the race checker that is closed on this pool (compute-sanitizer): the kernels' cross-block
     and cross-warp hand-offs -- the ticketed last-block reductions of k_schur / k_cost, the producer / consumer

@@ -950,7 +950,7 @@ void enqueue_eval(calib_handle* h, Launcher& ln) {
     const Dev& d = h->dev;
     cudaEvent_t a, b;
     ln.begin(&a, &b);
-    launch_iter(h, k_eval<MODEL>, d.ev_blocks, kEvalThreads, kEvalDynSmem, d);
+    launch_iter(h, k_eval<MODEL>, d.ev_blocks, kBlockThreads, kEvalDynSmem, d);
     ln.end(KEVAL, a, b);
     ln.count += 1;
 }
@@ -1342,7 +1342,7 @@ int lm_finish(calib_handle* h) {
     if (h->h_state->bar_abort) {
         char b[160];
         snprintf(b, sizeof b, "a wait inside the kernels timed out (code %d: 1 grid barrier of the persistent kernel, 2 / 3 / 4 "
-                              "hand-off of the evaluation pass: chain / intrinsic-sums / view-sums warp)", h->h_state->bar_abort);
+                              "hand-off of the evaluation pass: producer / consumer warp)", h->h_state->bar_abort);
         return fail(h, CALIB_E_CUDA, b);
     }
     float ms = 0;

@@ -218,6 +218,9 @@ __device__ __forceinline__ void accum_BD(const PointOut<MODEL>& o, double (&acc)
 // point as in accum_BD (bit-identical); only the order in which the inputs are touched differs: the
 // six extrinsic column pairs are held, the left factors stream through two at a time, so that 14
 // input values are live at once instead of 26 beside the 87 sums.
+template <int MODEL>
+__device__ __forceinline__ void accum_BD_j(const double2* slot, const double (&ju)[6], const double (&jv)[6], double (&acc)[kNBD]);
+
 // (jslot[j * 32] = (ju,jv)[j]: the same slot, or the second ring of the pipelined pass.)
 template <int MODEL>
 __device__ __forceinline__ void accum_BD_ring2(const double2* slot, const double2* jslot, double (&acc)[kNBD]) {
@@ -226,6 +229,14 @@ __device__ __forceinline__ void accum_BD_ring2(const double2* slot, const double
     double ju[6], jv[6];
 #pragma unroll
     for (int j = 0; j < 6; ++j) { const double2 t = jslot[j * 32]; ju[j] = t.x; jv[j] = t.y; }
+    accum_BD_j<MODEL>(slot, ju, jv, acc);
+}
+
+// ... with the extrinsic columns already in registers
+template <int MODEL>
+__device__ __forceinline__ void accum_BD_j(const double2* slot, const double (&ju)[6], const double (&jv)[6], double (&acc)[kNBD]) {
+    constexpr int ND = ModelTraits<MODEL>::ND, L = ModelTraits<MODEL>::L;
+    using S = SlotsBD<L>;
     {
         const double2 r = slot[1 * 32];                  // (ru, rv)
 #pragma unroll

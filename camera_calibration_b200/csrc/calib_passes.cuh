@@ -40,11 +40,9 @@ __device__ __forceinline__ PassCtx pass_ctx(const LmState& st) {
 
 // ---- the fused evaluation pass ----------------------------------------------------------------
 // A point's 2 x (L+6) Jacobian rows feed 143 running sums (56 of the intrinsic block A, g_c and the cost;
-// 87 of B_v, D_v, g_v): more than one thread can hold.  History (profiles/README.md): one warp sweeping the
-// points twice (416 FP64 instructions per point, 60.3 us at cfg3); producer / consumer warp PAIRS sharing one
-// sweep through a ring in shared memory (356 instructions, detections read once, 61.8 us: bound by the
-// producer's instruction stream, csrc/experiments/calib_eval_pairs.cuh); now warp TRIPLES with re-balanced
-// registers (58.3 us), below.  Per-lane accumulation order is the same in all three: bit-identical results.
+// 87 of B_v, D_v, g_v): more than one thread can hold.  Round 1 swept the points twice with one warp (the
+// projection chain evaluated twice: 416 FP64 instructions per point, the detections read twice beyond L2);
+// since round 2 a producer / consumer PAIR of warps shares ONE sweep (356 instructions, detections read once).
 constexpr int kEvalPairs = kBlockWarps / 2;
 constexpr int kEvalStages = 4;
 template <int MODEL> struct EvalRing {
@@ -54,7 +52,7 @@ template <int MODEL> struct EvalRing {
 constexpr size_t kEvalDynSmem = kEvalPairs * sizeof(EvalRing<0>);     // the radtan ring is the larger one
 
 struct __align__(16) EvalSmem {
-    ViewC sview[kEvalPairs];
+    ViewC sview[kEvalPairs], sviewA[kEvalPairs];    // the view constants of the chain warp / of the warp that finishes the extrinsic columns
     double sc[16];
     double sred[kEvalPairs][kNA];
     double sE[kEvalPairs];
@@ -92,52 +90,37 @@ __device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-// ---- warp triples with re-balanced registers ---------------------------------------------------------
-// ncu's source sampling of the pair kernel (profiles/r2f): one 32-point step took 1 570 cycles, the producer --
-// dependent projection chain AND the 57 sums of the intrinsic block, 352 instructions -- issued during 22 % of
-// them while the consumer slept on the hand-off.  Here the chain is a warp's ONLY work:
-//   P    (warps 0-3)   loads the point, runs point_eval, writes the hand-off slot -- no running sums;
-//   CA   (warps 4-7)   A, g_c and the cost (56 sums + 1) from pairs 0 .. 1+ND of the slot;
-//   CB   (warps 8-11)  B_v, D_v, g_v (87 sums) from all 8+ND pairs, one row per piece.
-// Warps t, t+4, t+8 share a scheduler and one ring (full: 1 arrival, empty: 2).  Three warps per scheduler
-// hold 168 registers each at launch; `setmaxnreg` moves them to where the sums live (radtan: P 112, CA 160,
-// CB 232; ptxas allocates per region, USETMAXREG in SASS; no spill).  A step now takes ~1 200 cycles
-// (profiles/r4c_eval3_ncu.md): P still bounds it -- 248 instructions at one issue per ~5 cycles (fixed-latency
-// dependencies 34 % of its samples) -- with the FP64 pipe 59 % busy.  Measured and rejected on top of this
-// (profiles/r4b, r4e): cutting the chain in two (P -> CA -> CB pipeline, experiments/calib_eval_pipeline.cuh:
-// slower, every warp of the scheduler then waits on the pipe), two steps per loop trip with swapped point
-// buffers (no gain), an L2 prefetch three steps ahead (-10 us on cold data, +1.4 us on L2-resident data), the
-// chain without its `valid` branch (lanes without a point computing on stale registers: 57.9 against 57.9 us).
-constexpr int kEvalThreads = 384;
-// per model: radtan carries 57 sums in CA and a shorter chain in P, fisheye 46 sums and the atan chain (no spill in either)
-template <int MODEL> struct EvalRegs;
-template <> struct EvalRegs<0> { static constexpr int P = 112, A = 160, B = 232; };
-template <> struct EvalRegs<1> { static constexpr int P = 128, A = 144, B = 232; };
-template <int N> __device__ __forceinline__ void reg_release() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
-template <int N> __device__ __forceinline__ void reg_acquire() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
-// from the 168 registers a thread of a 384-thread block starts with (dec above / inc below the current count is illegal)
-template <int N> __device__ __forceinline__ void reg_set() { if constexpr (N > 168) reg_acquire<N>(); else reg_release<N>(); }
+// ---- producer / consumer warp PAIRS ---------------------------------------------------------------------
+// A pair of warps (w, w + 4: same scheduler) shares one sweep over a chunk of points:
+//   producer   loads the point, runs the dependent projection chain, keeps the 57 sums of A, g_c, E and hands what the
+//              view blocks need to the consumer through a 4-stage ring in shared memory (one 16-byte slot per lane
+//              and value pair, lane-private, mbarrier full / empty per stage);
+//   consumer   keeps the 87 sums of B_v, D_v, g_v and writes one row per piece.
+// Since point_eval's reciprocal and reciprocal square root lost the special-case branch of __drcp_rn / rsqrt
+// (rcp_nr, rsqrt_nr in calib_device.cuh: the branch ended the basic block, nothing was scheduled into the ~70 cycles
+// of the operation), k_eval<radtan> takes 53.9 us at cfg3 instead of 61.8 us, bit-identical.
+// CUT (fisheye): the chain is cut after the distortion derivatives; the consumer finishes the extrinsic columns
+// (extrinsic_columns, 43 FP64 instructions) from six value pairs that replace the six (ju,jv) pairs in the slot.  The
+// fisheye chain is the longer one (rsqrt, atan): 309 -> 301 us at cfg5 x 0.2; radtan is faster uncut (53.9 against
+// 56.9 us).  Per-lane accumulation order is the same in every variant: bit-identical results.
+// What bounds it (profiles/README.md, r4n): an FP64 instruction holds a scheduler's issue port for two cycles and
+// other instructions do not hide behind it (micro/fp64_issue_mix.cu), so a 32-point step cannot take less than
+// 2 x 349 + ~0.9 x 187 = 866 cycles; it takes 1 100 (79 %).  Measured and rejected: warp TRIPLES with setmaxnreg
+// (chain / A sums / view sums in three warps, experiments/calib_eval_triples.cuh: 57.9 us -- it was the faster kernel
+// while the reciprocal still had its branch: 58.3 against 61.8 us), a three-stage pipeline (experiments/calib_eval_pipeline.cuh), producers and
+// consumers on different schedulers (60.5 us), two steps per trip, an L2 prefetch, the chain without its `valid` branch.
+template <int MODEL> struct EvalCut { static constexpr bool value = MODEL == 1; };
 
 template <int MODEL>
-__device__ __forceinline__ void accum_A_ring(const double2* slot, double (&acc)[kNA], double& e) {
-    constexpr int ND = ModelTraits<MODEL>::ND;
-    PointOut<MODEL> o;
-    { const double2 t = slot[0 * 32]; o.xd = t.x; o.yd = t.y; }
-    { const double2 t = slot[1 * 32]; o.ru = t.x; o.rv = t.y; }
-#pragma unroll
-    for (int a = 0; a < ND; ++a) { const double2 t = slot[(2 + a) * 32]; o.ku[a] = t.x; o.kv[a] = t.y; }
-    accum_A<MODEL>(o, acc, e);
-}
-
-template <int MODEL>
-__global__ void __launch_bounds__(kEvalThreads, 1) k_eval(Dev d) {
+__global__ void __launch_bounds__(kBlockThreads, 1) k_eval(Dev d) {
+    constexpr bool CUT = EvalCut<MODEL>::value;
     using T = ModelTraits<MODEL>;
-    constexpr int L = T::L, ND = T::ND, S = kEvalStages;
+    constexpr int L = T::L, ND = T::ND, S = kEvalStages, JM = 2 + ND;
     const int tid = threadIdx.x;
     const int lane = tid & 31, warp = tid >> 5;
-    const int trip = warp & (kEvalPairs - 1);
-    const int role = warp >> 2;                    // 0: P, 1: CA, 2: CB (warp-group uniform: setmaxnreg needs that)
-    const int w = blockIdx.x * kEvalPairs + trip;
+    const int pair = warp & (kEvalPairs - 1);
+    const bool producer = warp < kEvalPairs;
+    const int w = blockIdx.x * kEvalPairs + pair;
     WarpRec rec;
     rec.p0 = rec.p1 = 0;
     if (w < d.ev_warps) rec = d.ev_rec[w];
@@ -145,91 +128,74 @@ __global__ void __launch_bounds__(kEvalThreads, 1) k_eval(Dev d) {
     if (st->done || !st->need_eval) return;
     __shared__ EvalSmem sm;
     const int cur = st->cur;
-    EvalRing<MODEL>& ring = reinterpret_cast<EvalRing<MODEL>*>(dyn_smem)[trip];
-    unsigned long long* full = sm.full[trip];
-    unsigned long long* empty = sm.empty[trip];
+    EvalRing<MODEL>& ring = reinterpret_cast<EvalRing<MODEL>*>(dyn_smem)[pair];
+    unsigned long long* full = sm.full[pair];
+    unsigned long long* empty = sm.empty[pair];
     if (tid < L) sm.sc[tid] = d.Pbuf[(long long)cur * d.K + tid];
-    if (tid < kEvalPairs * S) { mbar_init(&sm.full[0][0] + tid, 1); mbar_init(&sm.empty[0][0] + tid, 2); }
+    if (tid < kEvalPairs * S) { mbar_init(&sm.full[0][0] + tid, 1); mbar_init(&sm.empty[0][0] + tid, 1); }
     if (tid == 0) mbar_fence_init();
     __syncthreads();
     const int p0 = rec.p0, p1 = rec.p1;
-    if (role == 0) {
-        // ---- P: the projection chain and the hand-off, nothing else
-        reg_release<EvalRegs<MODEL>::P>();
-        if (p0 >= p1) return;
-        const ViewC* views = d.views + (long long)cur * d.M;
-        Piece pc = rec.first;
-        Pt pn;
-        if (lane < pc.count) load_point(d, (long long)pc.start + lane, pn);
-        double vn = 0.0;
-        if (lane < kViewDoubles) vn = reinterpret_cast<const double*>(views + pc.view)[lane];
-        unsigned k = 0;                              // hand-offs so far
-        for (int pi = p0; pi < p1; ++pi) {
-            const bool has_next = pi + 1 < p1;
-            Piece nxt = pc;
-            if (has_next) nxt = d.ev_piece[pi + 1];
-            // the consumers never read sview: only this warp's own steps of the previous piece must be done
-            __syncwarp();
-            if (lane < kViewDoubles) reinterpret_cast<double*>(&sm.sview[trip])[lane] = vn;
-            __syncwarp();
-            if (has_next && lane < kViewDoubles) vn = reinterpret_cast<const double*>(views + nxt.view)[lane];
-            const int nsteps = (pc.count + 31) >> 5;
-            int idx = pc.start + lane;       // point indices fit 32 bits (Piece::start is an int)
-            int left = pc.count - lane;              // > 0: this lane has a point in the current step
-            // one step: the point in `p` is evaluated and handed off, the next one is fetched into `nx`
-            auto step = [&](const Pt& p, Pt& nx, bool last) {
-                const bool valid = left > 0;
-                left -= 32;
-                idx += 32;
-                if (!last) { if (left > 0) load_point(d, (long long)idx, nx); }
-                else if (has_next && lane < nxt.count) load_point(d, (long long)nxt.start + lane, nx);
-                const unsigned s = k % S;
-                if (k >= S) mbar_wait_guarded(&empty[s], ((k / S) - 1u) & 1u, d.st, 0);
-                if (valid) {
-                    PointOut<MODEL> o;
-                    point_eval<MODEL, true, true>(sm.sc, sm.sview[trip], p.X, p.Y, p.Z, p.U, p.V, o);
-                    double2* slot = &ring.v[s][0][lane];
-#pragma unroll
-                    for (int j = 0; j < 6; ++j) slot[(2 + ND + j) * 32] = make_double2(o.ju[j], o.jv[j]);
-                    slot[0 * 32] = make_double2(o.xd, o.yd);
-                    slot[1 * 32] = make_double2(o.ru, o.rv);
-#pragma unroll
-                    for (int a = 0; a < ND; ++a) slot[(2 + a) * 32] = make_double2(o.ku[a], o.kv[a]);
-                }
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&full[s]);
-                ++k;
-            };
-            for (int sidx = 0; sidx < nsteps; ++sidx) {
-                const Pt p = pn;
-                step(p, pn, sidx + 1 == nsteps);
-            }
-            pc = nxt;
-        }
-    } else if (role == 1) {
-        // ---- CA: intrinsic block, its right-hand side, the cost; then the block's row of partA / partE
-        reg_release<EvalRegs<MODEL>::A>();
+    const ViewC* views = d.views + (long long)cur * d.M;
+    if (producer) {
         double acc[kNA];
 #pragma unroll
         for (int i = 0; i < kNA; ++i) acc[i] = 0.0;
         double e = 0.0;
         if (p0 < p1) {
             Piece pc = rec.first;
-            int k = 0;
+            Pt pn;
+            if (lane < pc.count) load_point(d, (long long)pc.start + lane, pn);
+            double vn = 0.0;
+            if (lane < kViewDoubles) vn = reinterpret_cast<const double*>(views + pc.view)[lane];
+            unsigned k = 0;                              // hand-offs so far
             for (int pi = p0; pi < p1; ++pi) {
                 const bool has_next = pi + 1 < p1;
                 Piece nxt = pc;
                 if (has_next) nxt = d.ev_piece[pi + 1];
+                __syncwarp();
+                if (lane < kViewDoubles) reinterpret_cast<double*>(&sm.sview[pair])[lane] = vn;
+                __syncwarp();
+                if (has_next && lane < kViewDoubles) vn = reinterpret_cast<const double*>(views + nxt.view)[lane];
                 const int nsteps = (pc.count + 31) >> 5;
-                int left = pc.count - lane;
+                int idx = pc.start + lane;
+                int left = pc.count - lane;              // > 0: this lane has a point in the current step
                 for (int sidx = 0; sidx < nsteps; ++sidx) {
+                    const Pt p = pn;
                     const bool valid = left > 0;
                     left -= 32;
-                    const int s = k % S;
-                    mbar_wait_guarded(&full[s], (unsigned)(k / S) & 1u, d.st, 1);
-                    if (valid) accum_A_ring<MODEL>(&ring.v[s][0][lane], acc, e);
+                    idx += 32;
+                    if (sidx + 1 < nsteps) { if (left > 0) load_point(d, (long long)idx, pn); }
+                    else if (has_next && lane < nxt.count) load_point(d, (long long)nxt.start + lane, pn);
+                    const unsigned s = k % S;
+                    if (k >= S) mbar_wait_guarded(&empty[s], ((k / S) - 1u) & 1u, d.st, 0);
+                    PointOut<MODEL> o;
+                    if (valid) {
+                        double2* slot = &ring.v[s][0][lane];
+                        if constexpr (CUT) {
+                            PointMid m;
+                            point_eval<MODEL, true, 2>(sm.sc, sm.sview[pair], p.X, p.Y, p.Z, p.U, p.V, o, &m);
+                            slot[(JM + 0) * 32] = make_double2(m.dxx, m.dxy);
+                            slot[(JM + 1) * 32] = make_double2(m.dyy, m.iz);
+                            slot[(JM + 2) * 32] = make_double2(m.xn, m.yn);
+                            slot[(JM + 3) * 32] = make_double2(m.q0, m.q1);
+                            slot[(JM + 4) * 32] = make_double2(m.q2, p.Y);
+                            slot[(JM + 5) * 32] = make_double2(p.Z, 0.0);
+                        } else {
+                            point_eval<MODEL, true, 1>(sm.sc, sm.sview[pair], p.X, p.Y, p.Z, p.U, p.V, o);
+#pragma unroll
+                            for (int j = 0; j < 6; ++j) slot[(JM + j) * 32] = make_double2(o.ju[j], o.jv[j]);     // first: the extrinsic columns die here
+                        }
+                        slot[0 * 32] = make_double2(o.xd, o.yd);
+                        slot[1 * 32] = make_double2(o.ru, o.rv);
+#pragma unroll
+                        for (int a = 0; a < ND; ++a) slot[(2 + a) * 32] = make_double2(o.ku[a], o.kv[a]);
+                        if constexpr (CUT) accum_A<MODEL>(o, acc, e);      // measured: 301.4 against 303.7 us (cfg5 x 0.2)
+                    }
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&empty[s]);
+                    if (lane == 0) mbar_arrive(&full[s]);
+                    // uncut chain: the consumer is released first, the producer's own sums follow (53.9 against 56.8 us, cfg3)
+                    if constexpr (!CUT) { if (valid) accum_A<MODEL>(o, acc, e); }
                     ++k;
                 }
                 pc = nxt;
@@ -237,55 +203,78 @@ __global__ void __launch_bounds__(kEvalThreads, 1) k_eval(Dev d) {
         }
         warp_reduce_scatter<kNA>(acc, lane);
         e = warp_sum(e);
-        sm.sred[trip][2 * lane] = acc[0];
-        sm.sred[trip][2 * lane + 1] = acc[1];
-        if (lane == 0) sm.sE[trip] = e;
-        asm volatile("bar.sync 1, 128;" ::: "memory");       // the four CA warps
-        const int t = tid - 128;
-        if (t < kNA) {
-            double s = sm.sred[0][t];
-#pragma unroll
-            for (int q = 1; q < kEvalPairs; ++q) s += sm.sred[q][t];
-            d.partA[(long long)blockIdx.x * kNA + t] = s;
-        } else if (t == kNA) {
-            double s = sm.sE[0];
-#pragma unroll
-            for (int q = 1; q < kEvalPairs; ++q) s = __dadd_rn(s, sm.sE[q]);
-            d.partE[blockIdx.x] = s;
-        }
+        sm.sred[pair][2 * lane] = acc[0];
+        sm.sred[pair][2 * lane + 1] = acc[1];
+        if (lane == 0) sm.sE[pair] = e;
     } else {
-        // ---- CB: B_v, D_v, g_v -- one row of kNBD slots per piece
-        reg_acquire<EvalRegs<MODEL>::B>();
         double acc[kNBD];
 #pragma unroll
         for (int i = 0; i < kNBD; ++i) acc[i] = 0.0;
-        if (p0 >= p1) return;
-        Piece pc = rec.first;
-        int k = 0;
-        for (int pi = p0; pi < p1; ++pi) {
-            const bool has_next = pi + 1 < p1;
-            Piece nxt = pc;
-            if (has_next) nxt = d.ev_piece[pi + 1];
-            const int nsteps = (pc.count + 31) >> 5;
-            int left = pc.count - lane;
-            for (int sidx = 0; sidx < nsteps; ++sidx) {
-                const bool valid = left > 0;
-                left -= 32;
-                const int s = k % S;
-                mbar_wait_guarded(&full[s], (unsigned)(k / S) & 1u, d.st, 2);
-                if (valid) accum_BD_ring<MODEL>(&ring.v[s][0][lane], acc);
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&empty[s]);
-                ++k;
+        if (p0 < p1) {
+            Piece pc = rec.first;
+            double vn = 0.0;
+            if (CUT && lane < kViewDoubles) vn = reinterpret_cast<const double*>(views + pc.view)[lane];
+            unsigned k = 0;
+            for (int pi = p0; pi < p1; ++pi) {
+                const bool has_next = pi + 1 < p1;
+                Piece nxt = pc;
+                if (has_next) nxt = d.ev_piece[pi + 1];
+                if constexpr (CUT) {                     // its own copy of the view constants: it lags the producer by up to S steps
+                    __syncwarp();
+                    if (lane < kViewDoubles) reinterpret_cast<double*>(&sm.sviewA[pair])[lane] = vn;
+                    __syncwarp();
+                    if (has_next && lane < kViewDoubles) vn = reinterpret_cast<const double*>(views + nxt.view)[lane];
+                }
+                const int nsteps = (pc.count + 31) >> 5;
+                int left = pc.count - lane;
+                for (int sidx = 0; sidx < nsteps; ++sidx) {
+                    const bool valid = left > 0;
+                    left -= 32;
+                    const unsigned s = k % S;
+                    mbar_wait_guarded(&full[s], (k / S) & 1u, d.st, 1);
+                    if (valid) {
+                        const double2* slot = &ring.v[s][0][lane];
+                        if constexpr (CUT) {
+                            PointMid m;
+                            double Y, Z;
+                            { const double2 t = slot[(JM + 0) * 32]; m.dxx = t.x; m.dxy = t.y; }
+                            { const double2 t = slot[(JM + 1) * 32]; m.dyy = t.x; m.iz = t.y; }
+                            { const double2 t = slot[(JM + 2) * 32]; m.xn = t.x; m.yn = t.y; }
+                            { const double2 t = slot[(JM + 3) * 32]; m.q0 = t.x; m.q1 = t.y; }
+                            { const double2 t = slot[(JM + 4) * 32]; m.q2 = t.x; Y = t.y; }
+                            { const double2 t = slot[(JM + 5) * 32]; Z = t.x; }
+                            double ju[6], jv[6];
+                            extrinsic_columns(sm.sc, sm.sviewA[pair], m, Y, Z, ju, jv);
+                            accum_BD_j<MODEL>(slot, ju, jv, acc);
+                        } else {
+                            accum_BD_ring<MODEL>(slot, acc);
+                        }
+                    }
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&empty[s]);
+                    ++k;
+                }
+                warp_reduce_scatter<kNBD>(acc, lane);
+                double* row = d.partBD + (long long)pi * kNBD + lane * (kNBD / 32);
+#pragma unroll
+                for (int j = 0; j < kNBD / 32; ++j) row[j] = acc[j];
+#pragma unroll
+                for (int i = 0; i < kNBD; ++i) acc[i] = 0.0;
+                pc = nxt;
             }
-            warp_reduce_scatter<kNBD>(acc, lane);
-            double* row = d.partBD + (long long)pi * kNBD + lane * (kNBD / 32);
-#pragma unroll
-            for (int j = 0; j < kNBD / 32; ++j) row[j] = acc[j];
-#pragma unroll
-            for (int i = 0; i < kNBD; ++i) acc[i] = 0.0;
-            pc = nxt;
         }
+    }
+    __syncthreads();
+    if (tid < kNA) {
+        double s = sm.sred[0][tid];
+#pragma unroll
+        for (int q = 1; q < kEvalPairs; ++q) s += sm.sred[q][tid];
+        d.partA[(long long)blockIdx.x * kNA + tid] = s;
+    } else if (tid == kNA) {
+        double s = sm.sE[0];
+#pragma unroll
+        for (int q = 1; q < kEvalPairs; ++q) s = __dadd_rn(s, sm.sE[q]);
+        d.partE[blockIdx.x] = s;
     }
 }
 

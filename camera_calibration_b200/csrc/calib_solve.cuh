@@ -52,7 +52,7 @@ __device__ __forceinline__ double solve_dense_core(double* S, int lane) {
 #pragma unroll
     for (int j = 0; j < L; ++j) {
         const double dj = __shfl_sync(0xffffffffu, row[j], j);
-        const double id = rsqrt(dj);             // dj <= 0 or NaN poisons the step (rejected)
+        const double id = rsqrt_nr(dj);          // dj <= 0 or NaN poisons the step (rejected)
         inv[j] = id;
         const double lij = row[j] * id;
         row[j] = lij;

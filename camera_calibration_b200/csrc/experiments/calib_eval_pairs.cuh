@@ -5,6 +5,10 @@
 #pragma once
 #include "../calib_passes.cuh"
 
+#ifndef CALIB_PAIRS_SPLIT
+#define CALIB_PAIRS_SPLIT 0
+#endif
+
 namespace calib {
 
 // Block *vbp of the evaluation pass (pairs vb * 4 .. vb * 4 + 3 of the partition, rec = the record of
@@ -19,8 +23,14 @@ __device__ __forceinline__ void eval_block(const Dev& d, EvalSmem& sm, const vol
     constexpr int L = T::L, ND = T::ND, S = kEvalStages;
     const int tid = tid_now();
     const int lane = tid & 31, warp = tid >> 5;
+#if CALIB_PAIRS_SPLIT
+    // producers on schedulers 0 and 1 (warps 0, 1, 4, 5), consumers on schedulers 2 and 3 (warps 2, 3, 6, 7)
+    const int pair = (warp & 1) | ((warp >> 2) << 1);
+    const bool producer = (warp & 2) == 0;
+#else
     const int pair = warp & (kEvalPairs - 1);
     const bool producer = warp < kEvalPairs;
+#endif
     EvalRing<MODEL>& ring = reinterpret_cast<EvalRing<MODEL>*>(dyn_smem)[pair];
     unsigned long long* full = sm.full[pair];
     unsigned long long* empty = sm.empty[pair];
@@ -146,7 +156,11 @@ __device__ __forceinline__ void eval_block(const Dev& d, EvalSmem& sm, const vol
 
 template <int MODEL>
 __global__ void __launch_bounds__(kBlockThreads, 1) k_eval_pairs(Dev d) {
+#if CALIB_PAIRS_SPLIT
+    const int pair = ((threadIdx.x >> 5) & 1) | ((threadIdx.x >> 7) << 1);
+#else
     const int pair = (threadIdx.x >> 5) & (kEvalPairs - 1);
+#endif
     const int w = blockIdx.x * kEvalPairs + pair;
     WarpRec rec;                       // issued together with the state load below: one round trip
     rec.p0 = rec.p1 = 0;

@@ -5,9 +5,9 @@
 // step) and every one of them runs slower -- a step takes 1300 cycles, P waits on the FP64 pipe (math_pipe_throttle,
 // not_selected 19 % of its samples against 3 %), and the second ring adds 12 shared-memory transactions per point
 // to a pipe that already moves 528 B per point.  To build it: include this file after calib_passes.cuh, add the
-// function attributes (kEval4DynSmem) and a launch of k_eval4<MODEL> with kEvalThreads threads.
+// function attributes (kEval4DynSmem) and a launch of k_eval4<MODEL> with kEval3Threads threads.
 #pragma once
-#include "../calib_passes.cuh"
+#include "calib_eval_triples.cuh"
 
 namespace calib {
 
@@ -33,7 +33,7 @@ struct __align__(16) Eval4Smem {
 };
 
 template <int MODEL>
-__global__ void __launch_bounds__(kEvalThreads, 1) k_eval4(Dev d) {
+__global__ void __launch_bounds__(kEval3Threads, 1) k_eval4(Dev d) {
     using T = ModelTraits<MODEL>;
     constexpr int L = T::L, ND = T::ND, S = kEvalStages, JM = 2 + ND;     // JM: first slot of the mid values
     const int tid = threadIdx.x;

@@ -6,19 +6,6 @@
 #include <cuda_runtime.h>
 #include "../../camera_calibration_b200/csrc/calib_device.cuh"
 
-namespace calib {
-// the same for 1 / sqrt(x): NOT adopted -- it differs from libdevice's rsqrt in the last bit on 14 % of the inputs
-__device__ __forceinline__ double rsqrt_nr(double x) {
-    double y;
-    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
-    const double h = 0.5 * y;
-    double e = fma(-x * y, y, 1.0);
-    double z = fma(h, e, y);
-    e = fma(-x * z, z, 1.0);
-    z = fma(0.5 * z, e, z);
-    return x == 0.0 ? y : z;
-}
-}  // namespace calib
 
 __device__ uint64_t splitmix(uint64_t& s) {
     uint64_t z = (s += 0x9e3779b97f4a7c15ull);

@@ -46,7 +46,7 @@ __device__ __forceinline__ PassCtx pass_ctx(const LmState& st) {
 constexpr int kEvalPairs = kBlockWarps / 2;
 constexpr int kEvalStages = 4;
 template <int MODEL> struct EvalRing {
-    static constexpr int NV2 = 8 + ModelTraits<MODEL>::ND;      // (xd,yd) (ru,rv) (ku,kv)[ND] (ju,jv)[6]
+    static constexpr int NV2 = 8 + ModelTraits<MODEL>::ND;      // (xd,yd) (ru,rv) (ku,kv)[ND] (ju,jv)[6] -- or, chain cut: the 6 pairs the last stage starts from
     double2 v[kEvalStages][NV2][32];
 };
 constexpr size_t kEvalDynSmem = kEvalPairs * sizeof(EvalRing<0>);     // the radtan ring is the larger one
@@ -102,7 +102,7 @@ __device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
 // CUT (fisheye): the chain is cut after the distortion derivatives; the consumer finishes the extrinsic columns
 // (extrinsic_columns, 43 FP64 instructions) from six value pairs that replace the six (ju,jv) pairs in the slot.  The
 // fisheye chain is the longer one (rsqrt, atan): 309 -> 301 us at cfg5 x 0.2; radtan is faster uncut (53.9 against
-// 56.9 us).  Per-lane accumulation order is the same in every variant: bit-identical results.
+// 56.9 us cut, 55.4 us cut with the producer's sums after the signal: r4r).  Per-lane accumulation order is the same in every variant: bit-identical results.
 // What bounds it (profiles/README.md, r4n): an FP64 instruction holds a scheduler's issue port for two cycles and
 // other instructions do not hide behind it (micro/fp64_issue_mix.cu), so a 32-point step cannot take less than
 // 2 x 349 + ~0.9 x 187 = 866 cycles; it takes 1 100 (79 %).  Measured and rejected: warp TRIPLES with setmaxnreg

@@ -691,6 +691,11 @@ def bench_calibration(args, env, name, scale, steps, warmup, light=False):
                 "avg_launch_us": avg_s * 1e6, "avg_launch_us_after_l2_flush": cold_s * 1e6,
                 "frac_algorithmic_after_l2_flush": fl / cold_s / 1e12 / peak64,
                 "fp64_issue": issue,
+                # what the DFMA-only peak leaves out (micro-benchmark, not measured in this run)
+                "issue_port_note": "an FP64 instruction holds a scheduler's issue port for 2 cycles and other instructions "
+                                   "hide behind it only a little (profiles/r4n_fp64_issue_mix.txt): a 32-point step of a warp "
+                                   "pair (349 FP64 + 187 other warp instructions, radtan) needs >= ~866 cycles and takes "
+                                   "~1100 -- 0.79 of the issue bound at frac 0.60 of the DFMA-only rate (DESIGN.md 4.1)",
                 # the whole refinement as one launch: algorithmic work of all its sweeps / its duration
                 "whole_refinement": {
                     "kernel": "all kernels of the loop (k_eval, k_schur, k_backsub, k_cost inside the graph)",
